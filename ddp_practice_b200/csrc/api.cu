@@ -1,0 +1,550 @@
+// C ABI of libddpstep.so: context, launch sequence, CUDA-graph replay, peer bootstrap.
+// Declarations and the reference call each entry point stands in for: include/ddpstep.h
+#include "../../include/ddpstep.h"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "bwd_kernels.cuh"
+#include "fwd_kernels.cuh"
+#include "step_kernel.cuh"
+
+using namespace dstep;
+
+static thread_local std::string g_create_error;
+
+struct GraphEntry {
+  cudaGraphExec_t exec = nullptr;
+  cudaGraph_t graph = nullptr;
+  // the kernel nodes whose argument struct holds the input / label pointers, and host
+  // copies of those structs: a new (x, y) pair only re-points these nodes of the
+  // instantiated graph (cudaGraphExecKernelNodeSetParams), it does not re-capture
+  cudaGraphNode_t node_c1 = nullptr, node_fc = nullptr, node_c1w = nullptr;
+  Conv1Args a_c1;
+  FcArgs a_fc;
+  Conv1WgradArgs a_c1w;
+  const float* x = nullptr;
+  const int64_t* y = nullptr;
+  int n_kernels = 0;
+};
+
+struct ddpstep_ctx {
+  ddpstep_config cfg;
+  std::string err;
+  // state
+  float *params = nullptr, *grads = nullptr, *grads_scaled = nullptr, *bnbuf = nullptr;
+  long long* nbt = nullptr;
+  DevState* ds = nullptr;
+  BnStat* st = nullptr;  // [2]
+  float* counts = nullptr;
+  // activations (sized by batch_cap, element size by dtype)
+  void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
+  void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
+  float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
+  float* x_stage = nullptr;
+  int64_t* y_stage = nullptr;
+  // comm
+  SymRegion* sym = nullptr;
+  CommDev comm;
+  bool peers_ready = false;
+  std::vector<void*> opened;
+  // graphs, keyed by batch (train) / -batch (eval with labels) / -batch-100000 (eval, no labels)
+  std::map<long, GraphEntry> graphs;
+  cudaStream_t cap_stream = nullptr;
+  int64_t launches = 0;
+  int esize = 2;
+};
+
+static int fail(ddpstep_ctx* c, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return fail(ctx, DDPSTEP_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+template <typename P> static int dalloc(ddpstep_ctx* ctx, P** p, size_t bytes) {
+  CK(cudaMalloc(reinterpret_cast<void**>(p), bytes));
+  CK(cudaMemset(*p, 0, bytes));
+  return 0;
+}
+
+extern "C" void ddpstep_default_config(ddpstep_config* c) {
+  memset(c, 0, sizeof *c);
+  c->abi_version = DDPSTEP_ABI_VERSION;
+  c->rank = 0; c->world = 1; c->device = 0;
+  c->dtype = DDPSTEP_FP16;
+  c->batch_cap = 32;
+  c->use_scaler = 1; c->sync_bn = 1; c->use_graph = 1; c->conv_bias_double_round = 1;
+  c->lr = 1e-4f;
+  c->init_scale = 65536.0f; c->growth_factor = 2.0f; c->backoff_factor = 0.5f; c->growth_interval = 2000;
+  c->bn_momentum = 0.1f; c->bn_eps = 1e-5f;
+}
+
+extern "C" const char* ddpstep_last_error(const ddpstep_ctx* ctx) {
+  return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
+  ddpstep_ctx* ctx = nullptr;
+  if (!cfg || !out) return fail(nullptr, DDPSTEP_E_ARG, "null argument");
+  if (cfg->abi_version != DDPSTEP_ABI_VERSION) return fail(nullptr, DDPSTEP_E_ARG, "ABI version mismatch");
+  if (cfg->world < 1 || cfg->world > MAX_WORLD || cfg->rank < 0 || cfg->rank >= cfg->world)
+    return fail(nullptr, DDPSTEP_E_ARG, "bad rank/world %d/%d (world <= %d)", cfg->rank, cfg->world, MAX_WORLD);
+  if (cfg->batch_cap < 1) return fail(nullptr, DDPSTEP_E_ARG, "batch_cap must be >= 1");
+  if (cfg->dtype < 0 || cfg->dtype > 2) return fail(nullptr, DDPSTEP_E_ARG, "bad dtype");
+  CK(cudaSetDevice(cfg->device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major != 10)
+    return fail(nullptr, DDPSTEP_E_ARCH, "device %d is sm_%d%d; this library is built for sm_100a only", cfg->device,
+                prop.major, prop.minor);
+  ctx = new ddpstep_ctx();
+  ctx->cfg = *cfg;
+  ctx->esize = cfg->dtype == DDPSTEP_FP32 ? 4 : 2;
+  const size_t B = (size_t)cfg->batch_cap, es = (size_t)ctx->esize;
+  int rc = 0;
+#define A(p, bytes) if (!rc) rc = dalloc(ctx, &ctx->p, (bytes))
+  A(params, N_PAD * 4); A(grads, N_PAD * 4); A(grads_scaled, N_PAD * 4); A(bnbuf, N_BNBUF * 4);
+  A(nbt, 2 * 8); A(ds, sizeof(DevState)); A(st, 2 * sizeof(BnStat)); A(counts, 2 * 4);
+  A(y1, B * 16 * 784 * es); A(p1, B * 16 * 196 * es); A(y2, B * 32 * 196 * es); A(p2, B * 1568 * es);
+  A(logits, B * 10 * es); A(dlogits, B * 10 * es); A(dflat, B * 1568 * es); A(dy2, B * 32 * 196 * es);
+  A(dp1, B * 16 * 196 * es); A(nll, B * 4);
+  A(part1, 296 * 16 * 2 * 4); A(part2, 148 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
+  A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
+  A(x_stage, B * 784 * 4); A(y_stage, B * 8);
+  A(sym, sizeof(SymRegion));
+#undef A
+  if (rc) { g_create_error = ctx->err; ddpstep_destroy(ctx); return rc; }
+  // running_var starts at 1 (nn.BatchNorm2d), scaler at init_scale (grad_scaler.py:173-179)
+  std::vector<float> bn(N_BNBUF, 0.f);
+  for (int i = 0; i < 16; ++i) bn[BNB_RV1 + i] = 1.f;
+  for (int i = 0; i < 32; ++i) bn[BNB_RV2 + i] = 1.f;
+  DevState h;
+  memset(&h, 0, sizeof h);
+  h.scale = cfg->use_scaler ? cfg->init_scale : 1.0f;
+  cudaError_t e = cudaMemcpy(ctx->bnbuf, bn.data(), N_BNBUF * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(ctx->ds, &h, sizeof h, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking);
+  // kernels that need more than 48 KB of dynamic shared memory
+  const int smem_dgrad = (32 * 18 * C14_RS + 8 * 32 * 25) * 4, smem_c1w = (16 * 784 + 32 * C1_XS) * 4;
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<float, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__half, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__nv_bfloat16, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
+  if (e != cudaSuccess) {
+    fail(nullptr, DDPSTEP_E_CUDA, "context setup failed: %s", cudaGetErrorString(e));
+    ddpstep_destroy(ctx);
+    return DDPSTEP_E_CUDA;
+  }
+  memset(&ctx->comm, 0, sizeof ctx->comm);
+  ctx->comm.rank = cfg->rank;
+  ctx->comm.world = cfg->world;
+  ctx->comm.self = ctx->sym;
+  ctx->comm.peer[cfg->rank] = ctx->sym;
+  ctx->peers_ready = cfg->world == 1;
+  *out = ctx;
+  return 0;
+}
+
+static void drop_graphs(ddpstep_ctx* ctx) {
+  for (auto& kv : ctx->graphs) {
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    if (kv.second.graph) cudaGraphDestroy(kv.second.graph);
+  }
+  ctx->graphs.clear();
+}
+
+extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
+  if (!ctx) return 0;
+  cudaSetDevice(ctx->cfg.device);
+  cudaDeviceSynchronize();
+  drop_graphs(ctx);
+  for (void* p : ctx->opened) cudaIpcCloseMemHandle(p);
+  void* bufs[] = {ctx->params, ctx->grads, ctx->grads_scaled, ctx->bnbuf, ctx->nbt, ctx->ds, ctx->st, ctx->counts,
+                  ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->logits, ctx->dlogits, ctx->dflat, ctx->dy2, ctx->dp1,
+                  ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
+                  ctx->y_stage, ctx->sym};
+  for (void* p : bufs) if (p) cudaFree(p);
+  if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
+  delete ctx;
+  return 0;
+}
+
+extern "C" int ddpstep_export_handle(ddpstep_ctx* ctx, void* handle64) {
+  if (!ctx || !handle64) return fail(ctx, DDPSTEP_E_ARG, "null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == DDPSTEP_HANDLE_BYTES, "handle size");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaIpcMemHandle_t h;
+  CK(cudaIpcGetMemHandle(&h, ctx->sym));
+  memcpy(handle64, &h, sizeof h);
+  return 0;
+}
+
+extern "C" int ddpstep_import_peers(ddpstep_ctx* ctx, const void* handles, int32_t world) {
+  if (!ctx || !handles) return fail(ctx, DDPSTEP_E_ARG, "null argument");
+  if (world != ctx->cfg.world) return fail(ctx, DDPSTEP_E_ARG, "world %d != configured %d", world, ctx->cfg.world);
+  if (ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "peers already imported");
+  CK(cudaSetDevice(ctx->cfg.device));
+  for (int r = 0; r < world; ++r) {
+    if (r == ctx->cfg.rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const char*>(handles) + (size_t)r * DDPSTEP_HANDLE_BYTES, sizeof h);
+    void* p = nullptr;
+    CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    ctx->opened.push_back(p);
+    ctx->comm.peer[r] = static_cast<SymRegion*>(p);
+  }
+  ctx->peers_ready = true;
+  return 0;
+}
+
+extern "C" int ddpstep_load_state(ddpstep_ctx* ctx, const float* params, const float* bn, const int64_t* nbt) {
+  if (!ctx || !params || !bn) return fail(ctx, DDPSTEP_E_ARG, "null argument");
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(ctx->params, params, N_PARAM * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(ctx->bnbuf, bn, N_BNBUF * 4, cudaMemcpyHostToDevice));
+  int64_t z[2] = {0, 0};
+  CK(cudaMemcpy(ctx->nbt, nbt ? nbt : z, 16, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+extern "C" int ddpstep_read_state(ddpstep_ctx* ctx, float* params, float* bn, int64_t* nbt, float* scale,
+                                  int32_t* tracker) {
+  if (!ctx) return fail(ctx, DDPSTEP_E_ARG, "null argument");
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaDeviceSynchronize());
+  if (params) CK(cudaMemcpy(params, ctx->params, N_PARAM * 4, cudaMemcpyDeviceToHost));
+  if (bn) CK(cudaMemcpy(bn, ctx->bnbuf, N_BNBUF * 4, cudaMemcpyDeviceToHost));
+  if (nbt) CK(cudaMemcpy(nbt, ctx->nbt, 16, cudaMemcpyDeviceToHost));
+  DevState h;
+  CK(cudaMemcpy(&h, ctx->ds, sizeof h, cudaMemcpyDeviceToHost));
+  if (scale) *scale = h.scale;
+  if (tracker) *tracker = h.growth_tracker;
+  return 0;
+}
+
+extern "C" int ddpstep_set_scaler(ddpstep_ctx* ctx, float scale, int32_t tracker) {
+  if (!ctx) return fail(ctx, DDPSTEP_E_ARG, "null argument");
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(&ctx->ds->scale, &scale, 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(&ctx->ds->growth_tracker, &tracker, 4, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+extern "C" int ddpstep_state_ptrs(ddpstep_ctx* ctx, ddpstep_ptrs* o) {
+  if (!ctx || !o) return fail(ctx, DDPSTEP_E_ARG, "null argument");
+  o->params = ctx->params; o->grads = ctx->grads; o->grads_scaled = ctx->grads_scaled;
+  o->bn_buffers = ctx->bnbuf; o->num_batches_tracked = reinterpret_cast<int64_t*>(ctx->nbt);
+  o->scale = &ctx->ds->scale; o->growth_tracker = &ctx->ds->growth_tracker;
+  o->found_inf = &ctx->ds->found_inf; o->loss = &ctx->ds->loss;
+  o->logits = ctx->logits; o->counts = ctx->counts;
+  o->input_stage = ctx->x_stage; o->label_stage = ctx->y_stage;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ launch sequences
+
+static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+static inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+struct Recorder {  // keeps the argument structs that hold x / y so graph replays can be re-pointed
+  int n = 0;
+  Conv1Args a_c1;
+  FcArgs a_fc;
+  Conv1WgradArgs a_c1w;
+};
+
+template <typename T>
+static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
+  const ddpstep_config& cfg = c->cfg;
+  const int dbl = cfg.conv_bias_double_round, sync = cfg.sync_bn;
+  BnStat* st1 = c->st;
+  BnStat* st2 = c->st + 1;
+  auto mark = [&]() {
+    if (rec) rec->n++;
+    c->launches++;
+  };
+  // 1. conv1 + local BN1 statistics
+  const int g1 = std::min(B, 296);
+  Conv1Args a1{x, c->params, c->y1, c->part1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+  if (rec) rec->a_c1 = a1;
+  k_conv1_fwd<T><<<g1, 256, 0, s>>>(a1); mark();
+  // 2. BN1 + ReLU + pool
+  BnPoolArgs b1{c->y1, c->p1, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps};
+  k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
+  // 3. conv2 + local BN2 statistics
+  const int g2 = std::min(B, 148);
+  Conv14Args a2{c->p1, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+  k_conv14<T, 16, 32, 0><<<dim3(g2, 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2); mark();
+  // 4. BN2 + ReLU + pool
+  BnPoolArgs b2{c->y2, c->p2, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps};
+  k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
+  // 5. Linear + CE + dlogits + d(pool2 out)
+  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, c->dlogits, c->dflat, c->nll, c->counts,
+           c->ds, B, cfg.use_scaler, 0};
+  if (rec) rec->a_fc = f;
+  k_fc_ce<T><<<std::min(B, 296), 224, 0, s>>>(f); mark();
+  // 6. fc weight/bias gradient partials
+  const int nsf = clampi(cdiv(B, 8), 1, 40);
+  FcWgradArgs fw{c->p2, c->dlogits, c->gpart, B, cdiv(B, nsf)};
+  k_fc_wgrad<T><<<dim3(7, nsf), 224, 0, s>>>(fw); mark();
+  // 7/8. BN2 backward: reduce, then d(conv2 out)
+  const int ns2 = clampi(cdiv(B, 4), 1, 16);
+  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->dy2, c->gpart};
+  k_bn_bwd_reduce<T, 32, 14><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
+  k_bn2_bwd_apply<T><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
+  // 9. conv2 weight gradient partials, 10. conv2 data gradient
+  const int gw = std::min(B, 37);
+  Conv2WgradArgs w2{c->p1, c->dy2, c->gpart, B};
+  k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s>>>(w2); mark();
+  Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
+  k_conv14<T, 32, 16, 2><<<dim3(std::min(B, 296), 2), 128, (32 * 18 * C14_RS + 8 * 32 * 25) * 4, s>>>(d2); mark();
+  // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
+  const int ns1 = clampi(cdiv(B, 2), 1, 32);
+  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, nullptr, c->gpart};
+  k_bn_bwd_reduce<T, 16, 28><<<dim3(16, ns1), 256, 0, s>>>(r1); mark();
+  const int gc1 = std::min(B, 148);
+  Conv1WgradArgs cw{r1, x};
+  if (rec) rec->a_c1w = cw;
+  k_conv1_wgrad<T><<<gc1, 320, (16 * 784 + 32 * C1_XS) * 4, s>>>(cw); mark();
+  // 13. Reducer all-reduce + GradScaler + SGD
+  StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gdirect, c->nll, c->bnbuf, c->nbt, c->ds, c->comm, B,
+              gc1, gw, ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
+  k_step<T><<<STEP_CTAS, STEP_THREADS, 0, s>>>(sa); mark();
+  return cudaGetLastError();
+}
+
+template <typename T>
+static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
+  const ddpstep_config& cfg = c->cfg;
+  const int dbl = cfg.conv_bias_double_round;
+  auto mark = [&]() {
+    if (rec) rec->n++;
+    c->launches++;
+  };
+  Conv1Args a1{x, c->params, c->y1, nullptr, c->st, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
+  if (rec) rec->a_c1 = a1;
+  k_conv1_fwd<T><<<std::min(B, 296), 256, 0, s>>>(a1); mark();
+  BnPoolArgs b1{c->y1, c->p1, c->params, c->st, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 1, 0, cfg.bn_momentum, cfg.bn_eps};
+  k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
+  Conv14Args a2{c->p1, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
+  k_conv14<T, 16, 32, 0><<<dim3(std::min(B, 148), 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2); mark();
+  BnPoolArgs b2{c->y2, c->p2, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps};
+  k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
+  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1};
+  if (rec) rec->a_fc = f;
+  k_fc_ce<T><<<std::min(B, 296), 224, 0, s>>>(f); mark();
+  return cudaGetLastError();
+}
+
+template <bool TRAIN>
+static cudaError_t enqueue(ddpstep_ctx* c, const float* x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
+  switch (c->cfg.dtype) {
+    case DDPSTEP_FP32: return TRAIN ? enqueue_train<float>(c, x, y, B, s, rec) : enqueue_eval<float>(c, x, y, B, s, rec);
+    case DDPSTEP_FP16: return TRAIN ? enqueue_train<__half>(c, x, y, B, s, rec) : enqueue_eval<__half>(c, x, y, B, s, rec);
+    default: return TRAIN ? enqueue_train<__nv_bfloat16>(c, x, y, B, s, rec) : enqueue_eval<__nv_bfloat16>(c, x, y, B, s, rec);
+  }
+}
+
+struct KernelPtrs { const void *c1, *fc, *c1w; };
+static KernelPtrs kernel_ptrs(int dtype) {
+  switch (dtype) {
+    case DDPSTEP_FP32: return {(const void*)k_conv1_fwd<float>, (const void*)k_fc_ce<float>, (const void*)k_conv1_wgrad<float>};
+    case DDPSTEP_FP16: return {(const void*)k_conv1_fwd<__half>, (const void*)k_fc_ce<__half>, (const void*)k_conv1_wgrad<__half>};
+    default: return {(const void*)k_conv1_fwd<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16>, (const void*)k_conv1_wgrad<__nv_bfloat16>};
+  }
+}
+
+static int repoint(ddpstep_ctx* ctx, GraphEntry& ge, cudaGraphNode_t node, void* arg_struct) {
+  cudaKernelNodeParams kp;
+  CK(cudaGraphKernelNodeGetParams(node, &kp));
+  void* args[1] = {arg_struct};
+  kp.kernelParams = args;
+  kp.extra = nullptr;
+  CK(cudaGraphExecKernelNodeSetParams(ge.exec, node, &kp));
+  return 0;
+}
+
+// One captured graph per (mode, batch).  The step is launch- and latency-bound at batch 32,
+// so the 13 kernels are replayed with a single cudaGraphLaunch.
+template <bool TRAIN>
+static int run_graph(ddpstep_ctx* ctx, const float* x, const int64_t* y, int B, cudaStream_t s) {
+  const long key = TRAIN ? (long)B : (y ? -(long)B : -(long)B - 100000);
+  auto it = ctx->graphs.find(key);
+  if (it == ctx->graphs.end()) {
+    GraphEntry ge;
+    Recorder rec;
+    const int64_t before = ctx->launches;
+    CK(cudaStreamBeginCapture(ctx->cap_stream, cudaStreamCaptureModeThreadLocal));
+    cudaError_t e = enqueue<TRAIN>(ctx, x, y, B, ctx->cap_stream, &rec);
+    cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &ge.graph);
+    ctx->launches = before;
+    if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "launch during capture failed: %s", cudaGetErrorString(e));
+    if (e2 != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "graph capture failed: %s", cudaGetErrorString(e2));
+    CK(cudaGraphInstantiate(&ge.exec, ge.graph, 0));
+    size_t n = 0;
+    CK(cudaGraphGetNodes(ge.graph, nullptr, &n));
+    std::vector<cudaGraphNode_t> nodes(n);
+    CK(cudaGraphGetNodes(ge.graph, nodes.data(), &n));
+    const KernelPtrs kp = kernel_ptrs(ctx->cfg.dtype);
+    for (cudaGraphNode_t nd : nodes) {
+      cudaGraphNodeType ty;
+      CK(cudaGraphNodeGetType(nd, &ty));
+      if (ty != cudaGraphNodeTypeKernel) continue;
+      cudaKernelNodeParams p;
+      CK(cudaGraphKernelNodeGetParams(nd, &p));
+      if (p.func == kp.c1) ge.node_c1 = nd;
+      else if (p.func == kp.fc) ge.node_fc = nd;
+      else if (p.func == kp.c1w) ge.node_c1w = nd;
+    }
+    if (!ge.node_c1 || !ge.node_fc || (TRAIN && !ge.node_c1w))
+      return fail(ctx, DDPSTEP_E_STATE, "could not locate the input-consuming kernel nodes in the captured graph");
+    ge.a_c1 = rec.a_c1; ge.a_fc = rec.a_fc; ge.a_c1w = rec.a_c1w;
+    ge.x = x; ge.y = y; ge.n_kernels = rec.n;
+    it = ctx->graphs.emplace(key, ge).first;
+  }
+  GraphEntry& ge = it->second;
+  if (ge.x != x) {
+    ge.a_c1.x = x;
+    int rc = repoint(ctx, ge, ge.node_c1, &ge.a_c1);
+    if (rc) return rc;
+    if (TRAIN) {
+      ge.a_c1w.x = x;
+      rc = repoint(ctx, ge, ge.node_c1w, &ge.a_c1w);
+      if (rc) return rc;
+    }
+    ge.x = x;
+  }
+  if (ge.y != y) {
+    ge.a_fc.y = reinterpret_cast<const long long*>(y);
+    int rc = repoint(ctx, ge, ge.node_fc, &ge.a_fc);
+    if (rc) return rc;
+    ge.y = y;
+  }
+  CK(cudaGraphLaunch(ge.exec, s));
+  ctx->launches += ge.n_kernels;
+  return 0;
+}
+
+static int check_step_args(ddpstep_ctx* ctx, const void* x, int32_t batch) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  if (!x) return fail(ctx, DDPSTEP_E_ARG, "null input pointer");
+  if (batch < 1 || batch > ctx->cfg.batch_cap)
+    return fail(ctx, DDPSTEP_E_ARG, "batch %d outside [1, batch_cap=%d]", batch, ctx->cfg.batch_cap);
+  if (!ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "world > 1: call ddpstep_import_peers first");
+  return 0;
+}
+
+extern "C" int ddpstep_train_step(ddpstep_ctx* ctx, const float* x, const int64_t* y, int32_t batch, void* stream) {
+  int rc = check_step_args(ctx, x, batch);
+  if (rc) return rc;
+  if (!y) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (ctx->cfg.use_graph) return run_graph<true>(ctx, x, y, batch, s);
+  cudaError_t e = enqueue<true>(ctx, x, y, batch, s, nullptr);
+  if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* xh, const int64_t* yh, int32_t batch,
+                                       float* loss_out, void* stream) {
+  int rc = check_step_args(ctx, xh, batch);
+  if (rc) return rc;
+  if (!yh) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  CK(cudaMemcpyAsync(ctx->x_stage, xh, (size_t)batch * 784 * 4, cudaMemcpyHostToDevice, s));
+  CK(cudaMemcpyAsync(ctx->y_stage, yh, (size_t)batch * 8, cudaMemcpyHostToDevice, s));
+  rc = ddpstep_train_step(ctx, ctx->x_stage, ctx->y_stage, batch, stream);
+  if (rc) return rc;
+  if (loss_out) {
+    CK(cudaMemcpyAsync(loss_out, &ctx->ds->loss, 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+  }
+  return 0;
+}
+
+extern "C" int ddpstep_eval_batch(ddpstep_ctx* ctx, const float* x, const int64_t* y, int32_t batch, void* stream) {
+  int rc = check_step_args(ctx, x, batch);
+  if (rc) return rc;
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (ctx->cfg.use_graph) return run_graph<false>(ctx, x, y, batch, s);
+  cudaError_t e = enqueue<false>(ctx, x, y, batch, s, nullptr);
+  if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "eval launch failed: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int ddpstep_reset_counts(ddpstep_ctx* ctx, void* stream) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaMemsetAsync(ctx->counts, 0, 8, static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+extern "C" int ddpstep_reduce_counts(ddpstep_ctx* ctx, void* stream) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  if (!ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "world > 1: call ddpstep_import_peers first");
+  CK(cudaSetDevice(ctx->cfg.device));
+  CountsArgs a{ctx->counts, ctx->ds, ctx->comm};
+  k_reduce_counts<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  ctx->launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ddpstep_read_counts(ddpstep_ctx* ctx, float* correct, float* size, void* stream) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  CK(cudaSetDevice(ctx->cfg.device));
+  float h[2];
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  CK(cudaMemcpyAsync(h, ctx->counts, 8, cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  if (correct) *correct = h[0];
+  if (size) *size = h[1];
+  return 0;
+}
+
+extern "C" int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* host, int64_t bytes) {
+  if (!ctx || !host) return fail(ctx, DDPSTEP_E_ARG, "null argument");
+  const size_t B = (size_t)ctx->cfg.batch_cap, es = (size_t)ctx->esize;
+  const void* src[] = {ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->dlogits, ctx->dy2, ctx->dp1};
+  const size_t sz[] = {B * 16 * 784 * es, B * 16 * 196 * es, B * 32 * 196 * es, B * 1568 * es, B * 10 * es,
+                       B * 32 * 196 * es, B * 16 * 196 * es};
+  if (which < 0 || which > 6) return fail(ctx, DDPSTEP_E_ARG, "bad activation id %d", which);
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpy(host, src[which], std::min((size_t)bytes, sz[which]), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+extern "C" int64_t ddpstep_launch_count(const ddpstep_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int ddpstep_device_status(ddpstep_ctx* ctx) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  CK(cudaSetDevice(ctx->cfg.device));
+  CK(cudaDeviceSynchronize());
+  DevState h;
+  CK(cudaMemcpy(&h, ctx->ds, sizeof h, cudaMemcpyDeviceToHost));
+  if (h.error) return fail(ctx, DDPSTEP_E_PEER, "a peer did not raise its flag within the spin timeout");
+  return 0;
+}

@@ -1,0 +1,384 @@
+// Backward kernels of the ConvNet step (direct, CUDA-core path; any batch size).
+// Autograd of ddp_main.py:91 `scaler.scale(loss).backward()` through ddp_main.py:16-28.
+// ReLU masks and max-pool winners are recomputed from the saved conv outputs and the BN
+// statistics instead of being stored (the reference keeps int64 pool indices, 4x the data).
+#pragma once
+#include "fwd_kernels.cuh"
+
+namespace dstep {
+
+// The four BN outputs of one 2x2 pooling window and who wins the pool.
+// Winner = first maximum of the ReLU outputs in scan order (max_pool2d_with_indices);
+// gradient flows only if the winner's ReLU output is > 0 (threshold_backward).
+template <typename T>
+__device__ __forceinline__ int pool_winner(const float y[4], float mu, float is, float g, float b, bool& live) {
+  float best = -1.f;
+  int arg = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float r = fmaxf(rnd<T>((y[i] - mu) * is * g + b), 0.f);
+    if (r > best) { best = r; arg = i; }
+  }
+  live = best > 0.f;
+  return arg;
+}
+
+// ---------------------------------------------------------------------------------------
+// fc weight / bias gradient: dW[j][k] = sum_n dlogits[n][j] * p2[n][k], db[j] = sum_n dlogits[n][j]
+// grid (7 k-chunks of 224, NS batch splits); partial rows go to gpart[split].
+struct FcWgradArgs {
+  const void* p2;
+  const void* dlogits;
+  float* gpart;  // [rows][N_PAD]
+  int B, per_split;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(224) k_fc_wgrad(FcWgradArgs a) {
+  __shared__ float dl_s[32][10];
+  const int tid = threadIdx.x;
+  const int k = blockIdx.x * 224 + tid;
+  const int n0 = blockIdx.y * a.per_split;
+  const int n1 = min(a.B, n0 + a.per_split);
+  const T* __restrict__ p2 = reinterpret_cast<const T*>(a.p2);
+  const T* __restrict__ dl = reinterpret_cast<const T*>(a.dlogits);
+  float acc[10], bsum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 10; ++j) acc[j] = 0.f;
+  for (int nb = n0; nb < n1; nb += 32) {
+    const int cnt = min(32, n1 - nb);
+    __syncthreads();
+    for (int i = tid; i < cnt * 10; i += 224) dl_s[i / 10][i % 10] = ldf<T>(&dl[(size_t)nb * 10 + i]);
+    __syncthreads();
+    for (int i = 0; i < cnt; ++i) {
+      const float x = ldf<T>(&p2[(size_t)(nb + i) * 1568 + k]);
+#pragma unroll
+      for (int j = 0; j < 10; ++j) acc[j] = fmaf(dl_s[i][j], x, acc[j]);
+    }
+    if (blockIdx.x == 0 && tid < 10)
+      for (int i = 0; i < cnt; ++i) bsum += dl_s[i][tid];
+  }
+  float* row = a.gpart + (size_t)blockIdx.y * N_PAD;
+#pragma unroll
+  for (int j = 0; j < 10; ++j) row[OFF_WFC + j * 1568 + k] = acc[j];
+  if (blockIdx.x == 0 && tid < 10) row[OFF_BFC + tid] = bsum;
+}
+
+// ---------------------------------------------------------------------------------------
+// BN backward, pass 1 (`batch_norm_backward_reduce`, _functions.py:144): per channel
+// sum(dy) and sum(dy * (x - mean)) where dy is the gradient arriving at the BN output, i.e.
+// d(pool out) routed through max-pool and ReLU.  grid (C, NS).  The last CTA turns the
+// partials into this rank's sums, writes d(gamma), d(beta), and under SyncBN pushes the
+// sums to every rank (the all_reduce of _functions.py:159).
+struct BnBwdArgs {
+  const void* y;      // conv output [B,C,H,H]
+  const void* dpool;  // gradient at the pool output [B,C,H/2,H/2]
+  const float* params;
+  BnStat* st;
+  float* bpart;       // [C][NS][2]
+  float* gdirect;     // [N_PAD] fp32 gradients written without partials (BN gamma/beta)
+  DevState* ds;
+  CommDev comm;
+  int B, per_split, layer, sync;
+  // pass 2 only
+  void* dy;           // [B,C,H,H] gradient at the conv output
+  float* gpart;       // conv-bias gradient partial rows
+};
+
+template <typename T, int C, int H>
+__global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
+  constexpr int HP = H / 2;
+  constexpr int OFF_G = (C == 16) ? OFF_G1 : OFF_G2, OFF_BE = (C == 16) ? OFF_BE1 : OFF_BE2;
+  __shared__ float red[8][2];
+  const int tid = threadIdx.x, c = blockIdx.x;
+  const int n0 = blockIdx.y * a.per_split, n1 = min(a.B, n0 + a.per_split);
+  const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
+  const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
+  const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G + c], b = a.params[OFF_BE + c];
+  float sdy = 0.f, sdyx = 0.f;
+  const int total = max(0, n1 - n0) * HP * HP;
+  for (int e = tid; e < total; e += 256) {
+    const int n = n0 + e / (HP * HP), w = e % (HP * HP), ph = w / HP, pw = w % HP;
+    const T* src = y + (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
+    float v[4];
+    load2<T>(src, v[0], v[1]);
+    load2<T>(src + H, v[2], v[3]);
+    bool live;
+    const int arg = pool_winner<T>(v, mu, is, g, b, live);
+    if (live) {
+      const float d = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
+      sdy += d;
+      sdyx = fmaf(d, v[arg] - mu, sdyx);
+    }
+  }
+  sdy = warp_sum(sdy);
+  sdyx = warp_sum(sdyx);
+  if ((tid & 31) == 0) { red[tid >> 5][0] = sdy; red[tid >> 5][1] = sdyx; }
+  __syncthreads();
+  if (tid < 2) {
+    float v = 0.f;
+    for (int w = 0; w < 8; ++w) v += red[w][tid];
+    a.bpart[((size_t)c * gridDim.y + blockIdx.y) * 2 + tid] = v;
+  }
+  if (last_cta_done(&a.ds->ticket[2 + a.layer], gridDim.x * gridDim.y)) {
+    const bool xchg = a.sync && a.comm.world > 1;
+    if (tid < C) {
+      double s0 = 0.0, s1 = 0.0;
+      for (int s = 0; s < (int)gridDim.y; ++s) {
+        s0 += (double)__ldcg(&a.bpart[((size_t)tid * gridDim.y + s) * 2]);
+        s1 += (double)__ldcg(&a.bpart[((size_t)tid * gridDim.y + s) * 2 + 1]);
+      }
+      const float f0 = (float)s0, f1 = (float)s1;
+      a.st->lsum_dy[tid] = f0;
+      a.st->lsum_dy_xmu[tid] = f1;
+      a.gdirect[OFF_G + tid] = f1 * a.st->invstd[tid];  // d(gamma), local: DDP averages it
+      a.gdirect[OFF_BE + tid] = f0;                      // d(beta)
+      if (xchg) {
+        for (int q = 0; q < a.comm.world; ++q) {
+          float* slot = a.comm.peer[q]->slot_bn_bwd[a.layer][a.comm.rank];
+          slot[tid] = f0;
+          slot[C + tid] = f1;
+        }
+      }
+    }
+    if (xchg) {
+      __threadfence_system();
+      __syncthreads();
+      if (tid < a.comm.world)
+        st_release_sys(&a.comm.peer[tid]->flag_bn[2 + (1 - a.layer)][a.comm.rank], a.ds->epoch + 1ull);
+    }
+  }
+}
+
+// Global (all-rank) backward sums for the consumer of pass 1: k1 = sum_dy / N,
+// k2 = invstd^2 * sum_dy_xmu / N  (`batch_norm_backward_elemt`, _functions.py:170).
+template <int C>
+__device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
+  const int c = threadIdx.x;
+  const bool xchg = a.sync && a.comm.world > 1;
+  if (xchg) {
+    if (c < a.comm.world)
+      wait_flag(&a.comm.self->flag_bn[2 + (1 - a.layer)][c], a.ds->epoch + 1ull, &a.ds->error);
+    __syncthreads();
+  }
+  if (c < C) {
+    float s0, s1;
+    if (xchg) {
+      s0 = 0.f; s1 = 0.f;
+      for (int r = 0; r < a.comm.world; ++r) {
+        const float* slot = a.comm.self->slot_bn_bwd[a.layer][r];
+        s0 += __ldcg(&slot[c]);
+        s1 += __ldcg(&slot[C + c]);
+      }
+    } else {
+      s0 = a.st->lsum_dy[c];
+      s1 = a.st->lsum_dy_xmu[c];
+    }
+    const float n = a.st->n_total, is = a.st->invstd[c];
+    s_k1[c] = s0 / n;
+    s_k2[c] = is * is * s1 / n;
+  }
+  __syncthreads();
+}
+
+// BN backward, pass 2 for layer 2: d(conv2 out) materialised (it feeds both conv2 dgrad and
+// wgrad); also the conv2 bias gradient partials (sum of the rounded values).  grid (32, NS).
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
+  constexpr int C = 32, H = 14, HP = 7;
+  __shared__ float s_k1[C], s_k2[C];
+  __shared__ float red[8];
+  bn_backward_sums<C>(a, s_k1, s_k2);
+  const int tid = threadIdx.x, c = blockIdx.x;
+  const int n0 = blockIdx.y * a.per_split, n1 = min(a.B, n0 + a.per_split);
+  const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
+  const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
+  T* __restrict__ dy = reinterpret_cast<T*>(a.dy);
+  const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G2 + c], b = a.params[OFF_BE2 + c];
+  const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
+  float bsum = 0.f;
+  const int total = max(0, n1 - n0) * HP * HP;
+  for (int e = tid; e < total; e += 256) {
+    const int n = n0 + e / (HP * HP), w = e % (HP * HP), ph = w / HP, pw = w % HP;
+    const size_t off = (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
+    float v[4];
+    load2<T>(y + off, v[0], v[1]);
+    load2<T>(y + off + H, v[2], v[3]);
+    bool live;
+    const int arg = pool_winner<T>(v, mu, is, g, b, live);
+    const float d = live ? ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]) : 0.f;
+    float o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float da = (live && i == arg) ? d : 0.f;
+      o[i] = rnd<T>((da - k1 - (v[i] - mu) * k2) * k3);
+      bsum += o[i];
+    }
+    store2<T>(dy + off, o[0], o[1]);
+    store2<T>(dy + off + H, o[2], o[3]);
+  }
+  bsum = warp_sum(bsum);
+  if ((tid & 31) == 0) red[tid >> 5] = bsum;
+  __syncthreads();
+  if (tid == 0) {
+    float v = 0.f;
+    for (int w = 0; w < 8; ++w) v += red[w];
+    a.gpart[(size_t)blockIdx.y * N_PAD + OFF_B2 + c] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// conv2 weight gradient: dW[co][ci][kh][kw] = sum_{n,h,w} dy2[n,co,h,w] * p1[n,ci,h+kh-2,w+kw-2]
+// grid (GX images-strided, 4 groups of 8 output channels), 160 threads = 16 ci x 5 kh x 2
+// quads of co; each thread owns a 5 (kw) x 4 (co) register tile over all its images.
+struct Conv2WgradArgs {
+  const void* p1;   // [B,16,14,14]
+  const void* dy2;  // [B,32,14,14]
+  float* gpart;     // [rows = gridDim.x][N_PAD]
+  int B;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(160) k_conv2_wgrad(Conv2WgradArgs a) {
+  __shared__ __align__(16) float in_s[16 * 18 * C14_RS];
+  __shared__ __align__(16) float dy_s[196 * 8];
+  const int tid = threadIdx.x, cog = blockIdx.y;
+  const int coq = tid & 1, r = tid >> 1, kh = r % 5, ci = r / 5;
+  const T* __restrict__ p1 = reinterpret_cast<const T*>(a.p1);
+  const T* __restrict__ dy2 = reinterpret_cast<const T*>(a.dy2);
+  for (int i = tid; i < 16 * 18 * C14_RS; i += 160) in_s[i] = 0.f;
+  float acc[5][4];
+#pragma unroll
+  for (int k = 0; k < 5; ++k)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[k][j] = 0.f;
+
+  for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
+    __syncthreads();
+    for (int i = tid; i < 16 * 196; i += 160) {
+      const int c = i / 196, rr = (i % 196) / 14, cc = i % 14;
+      in_s[(c * 18 + rr + 2) * C14_RS + cc + 2] = ldf<T>(&p1[(size_t)n * 16 * 196 + i]);
+    }
+    for (int i = tid; i < 8 * 196; i += 160) {
+      const int cl = i / 196, pix = i % 196;
+      dy_s[pix * 8 + cl] = ldf<T>(&dy2[((size_t)n * 32 + cog * 8 + cl) * 196 + pix]);
+    }
+    __syncthreads();
+    for (int h = 0; h < 14; ++h) {
+      float xr[18];
+      const float* xrow = in_s + (ci * 18 + h + kh) * C14_RS;
+#pragma unroll
+      for (int c = 0; c < 18; ++c) xr[c] = xrow[c];
+#pragma unroll
+      for (int w = 0; w < 14; ++w) {
+        const float4 d = *reinterpret_cast<const float4*>(&dy_s[(h * 14 + w) * 8 + coq * 4]);
+#pragma unroll
+        for (int kw = 0; kw < 5; ++kw) {
+          acc[kw][0] = fmaf(xr[w + kw], d.x, acc[kw][0]);
+          acc[kw][1] = fmaf(xr[w + kw], d.y, acc[kw][1]);
+          acc[kw][2] = fmaf(xr[w + kw], d.z, acc[kw][2]);
+          acc[kw][3] = fmaf(xr[w + kw], d.w, acc[kw][3]);
+        }
+      }
+    }
+  }
+  float* row = a.gpart + (size_t)blockIdx.x * N_PAD;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int kw = 0; kw < 5; ++kw)
+      row[OFF_W2 + ((cog * 8 + coq * 4 + j) * 16 + ci) * 25 + kh * 5 + kw] = acc[kw][j];
+}
+
+// ---------------------------------------------------------------------------------------
+// BN1 backward pass 2 fused with the conv1 weight / bias gradient (conv1's input needs no
+// gradient, so d(conv1 out) lives only in shared memory):
+//   dW1[co][kh][kw] = sum_{n,h,w} dy1[n,co,h,w] * x[n,h+kh-2,w+kw-2],  db1[co] = sum dy1
+// 320 threads: phase A one pooling window per thread-iteration, phase B thread = (co, kh,
+// quarter of the rows) with a 5-wide kw register tile.
+struct Conv1WgradArgs {
+  BnBwdArgs bn;    // y = y1, dpool = d(pool1 out), layer = 0
+  const float* x;  // [B,784] fp32
+};
+
+template <typename T>
+__global__ void __launch_bounds__(320) k_conv1_wgrad(Conv1WgradArgs a) {
+  extern __shared__ __align__(16) float smem[];
+  float* dy_s = smem;                // [16][28][28]
+  float* xs = smem + 16 * 784;       // [32][C1_XS]
+  __shared__ float s_k1[16], s_k2[16], s_mu[16], s_is[16], s_g[16], s_b[16];
+  bn_backward_sums<16>(a.bn, s_k1, s_k2);
+  const int tid = threadIdx.x;
+  if (tid < 16) {
+    s_mu[tid] = a.bn.st->mean[tid];
+    s_is[tid] = a.bn.st->invstd[tid];
+    s_g[tid] = a.bn.params[OFF_G1 + tid];
+    s_b[tid] = a.bn.params[OFF_BE1 + tid];
+  }
+  for (int i = tid; i < 32 * C1_XS; i += 320) xs[i] = 0.f;
+  const T* __restrict__ y1 = reinterpret_cast<const T*>(a.bn.y);
+  const T* __restrict__ dp1 = reinterpret_cast<const T*>(a.bn.dpool);
+  const int rs = tid & 3, kh = (tid >> 2) % 5, co = tid / 20;
+  float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f}, bsum = 0.f;
+
+  for (int n = blockIdx.x; n < a.bn.B; n += gridDim.x) {
+    __syncthreads();
+    for (int i = tid; i < 784; i += 320) xs[(i / 28 + 2) * C1_XS + i % 28 + 2] = rnd<T>(a.x[(size_t)n * 784 + i]);
+    for (int e = tid; e < 16 * 196; e += 320) {
+      const int c = e / 196, w = e % 196, ph = w / 14, pw = w % 14;
+      const size_t off = (((size_t)n * 16 + c) * 28 + 2 * ph) * 28 + 2 * pw;
+      float v[4];
+      load2<T>(y1 + off, v[0], v[1]);
+      load2<T>(y1 + off + 28, v[2], v[3]);
+      const float mu = s_mu[c], is = s_is[c], g = s_g[c];
+      bool live;
+      const int arg = pool_winner<T>(v, mu, is, g, s_b[c], live);
+      const float d = live ? ldf<T>(&dp1[((size_t)n * 16 + c) * 196 + w]) : 0.f;
+      const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
+      float o[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float da = (live && i == arg) ? d : 0.f;
+        o[i] = rnd<T>((da - k1 - (v[i] - mu) * k2) * k3);
+      }
+      float* dst = dy_s + (c * 28 + 2 * ph) * 28 + 2 * pw;
+      dst[0] = o[0]; dst[1] = o[1]; dst[28] = o[2]; dst[29] = o[3];
+    }
+    __syncthreads();
+    for (int h = rs * 7; h < rs * 7 + 7; ++h) {
+      const float* drow = dy_s + (co * 28 + h) * 28;
+      const float* xrow = xs + (h + kh) * C1_XS;
+#pragma unroll
+      for (int q = 0; q < 7; ++q) {
+        const float4 d = *reinterpret_cast<const float4*>(drow + 4 * q);
+        const float4 u = *reinterpret_cast<const float4*>(xrow + 4 * q);
+        const float4 v = *reinterpret_cast<const float4*>(xrow + 4 * q + 4);
+        const float xv[8] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int kw = 0; kw < 5; ++kw) {
+          acc[kw] = fmaf(d.x, xv[kw], acc[kw]);
+          acc[kw] = fmaf(d.y, xv[kw + 1], acc[kw]);
+          acc[kw] = fmaf(d.z, xv[kw + 2], acc[kw]);
+          acc[kw] = fmaf(d.w, xv[kw + 3], acc[kw]);
+        }
+        if (kh == 0) bsum += (d.x + d.y) + (d.z + d.w);
+      }
+    }
+  }
+  // reduce over the 4 row-quarters (adjacent lanes)
+#pragma unroll
+  for (int kw = 0; kw < 5; ++kw) {
+    acc[kw] += __shfl_xor_sync(0xffffffffu, acc[kw], 1);
+    acc[kw] += __shfl_xor_sync(0xffffffffu, acc[kw], 2);
+  }
+  bsum += __shfl_xor_sync(0xffffffffu, bsum, 1);
+  bsum += __shfl_xor_sync(0xffffffffu, bsum, 2);
+  if (rs == 0) {
+    float* row = a.bn.gpart + (size_t)blockIdx.x * N_PAD;
+#pragma unroll
+    for (int kw = 0; kw < 5; ++kw) row[OFF_W1 + co * 25 + kh * 5 + kw] = acc[kw];
+    if (kh == 0) row[OFF_B1 + co] = bsum;
+  }
+}
+
+}  // namespace dstep

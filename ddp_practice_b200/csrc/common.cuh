@@ -1,0 +1,140 @@
+// Shared device-side definitions of the fused ConvNet DDP+AMP step (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dstep {
+
+// ---- flat parameter / gradient bucket layout (definition order, ddp_main.py:16-28) ----
+constexpr int N_PARAM = 29034;
+constexpr int N_PAD = 29056;  // padded row length of every bucket-shaped buffer (multiple of 32)
+constexpr int OFF_W1 = 0, OFF_B1 = 400, OFF_G1 = 416, OFF_BE1 = 432;
+constexpr int OFF_W2 = 448, OFF_B2 = 13248, OFF_G2 = 13280, OFF_BE2 = 13312;
+constexpr int OFF_WFC = 13344, OFF_BFC = 29024;
+// BN buffer block: rm1[16] rv1[16] rm2[32] rv2[32]
+constexpr int BNB_RM1 = 0, BNB_RV1 = 16, BNB_RM2 = 32, BNB_RV2 = 64, N_BNBUF = 96;
+
+constexpr int MAX_WORLD = 8;
+constexpr int STEP_CTAS = 8;        // one cluster
+constexpr int STEP_THREADS = 1024;  // 8 * 1024 * 4 = 32768 >= N_PAD
+constexpr int MAX_PART_ROWS = 160;  // rows of the weight-gradient partial buffer
+
+// ---- storage dtype helpers -------------------------------------------------------------
+template <typename T> struct Cvt;
+template <> struct Cvt<float> {
+  static __device__ __forceinline__ float to_f(float v) { return v; }
+  static __device__ __forceinline__ float from_f(float v) { return v; }
+};
+template <> struct Cvt<__half> {
+  static __device__ __forceinline__ float to_f(__half v) { return __half2float(v); }
+  static __device__ __forceinline__ __half from_f(float v) { return __float2half_rn(v); }
+};
+template <> struct Cvt<__nv_bfloat16> {
+  static __device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+  static __device__ __forceinline__ __nv_bfloat16 from_f(float v) { return __float2bfloat16_rn(v); }
+};
+// round an fp32 value to the storage dtype and come back (the autocast rounding point)
+template <typename T> __device__ __forceinline__ float rnd(float v) { return Cvt<T>::to_f(Cvt<T>::from_f(v)); }
+template <typename T> __device__ __forceinline__ float ldf(const T* p) { return Cvt<T>::to_f(*p); }
+template <typename T> __device__ __forceinline__ void stf(T* p, float v) { *p = Cvt<T>::from_f(v); }
+
+// conv output epilogue: cudnn_convolution rounds, then add_(bias) rounds again (dbl = 1)
+template <typename T> __device__ __forceinline__ float conv_out(float acc, float bias_r, int dbl) {
+  return rnd<T>((dbl ? rnd<T>(acc) : acc) + bias_r);
+}
+
+// ---- cross-GPU symmetric region (identical layout on every rank) -----------------------
+// Exchanges are PUSH: the producer stores into every consumer's region and then raises a
+// flag there; consumers spin on their own memory only.  Flags carry a monotonically
+// increasing epoch (never reset), so a stale flag can never satisfy a later wait.
+struct SymRegion {
+  // flags[x][r]: rank r finished pushing exchange x for epoch == value
+  unsigned long long flag_bn[4][MAX_WORLD];                // 0 bn1 fwd, 1 bn2 fwd, 2 bn2 bwd, 3 bn1 bwd
+  unsigned long long flag_grad[MAX_WORLD][STEP_CTAS];      // per sender rank, per chunk (CTA)
+  unsigned long long flag_counts[MAX_WORLD];
+  unsigned long long flag_counts_ack;                      // rank 0 consumed this rank's counters
+  float slot_bn_fwd[2][MAX_WORLD][68];                     // mean[C] invstd[C] count   (C <= 32)
+  float slot_bn_bwd[2][MAX_WORLD][64];                     // sum_dy[C] sum_dy_xmu[C]
+  float slot_counts[MAX_WORLD][2];
+  float slot_bnbuf[N_BNBUF];                               // rank 0's running buffers (plain-BN DDP)
+  long long slot_nbt[2];
+  float inbox[2][MAX_WORLD][N_PAD];                        // [step parity][sender rank][bucket]
+};
+
+struct CommDev {
+  int rank, world;
+  SymRegion* self;
+  SymRegion* peer[MAX_WORLD];  // peer[rank] == self
+};
+
+// device-resident step state
+struct DevState {
+  unsigned long long epoch;       // completed training steps (flag value base)
+  unsigned long long eval_epoch;  // completed count reductions
+  unsigned int ticket[8];         // "last CTA finishes" counters, one per producing kernel
+  int error;                      // 0 ok, 1 peer timeout
+  float scale;
+  int growth_tracker;
+  float found_inf;
+  float loss;
+};
+
+// global BN statistics of the current step, written by the bn_relu_pool kernel
+struct BnStat {
+  float mean[32];
+  float invstd[32];
+  float n_total;
+  // local (this rank) statistics from the conv epilogue
+  float lmean[32];
+  float linvstd[32];
+  float lvar_unbiased[32];
+  // backward sums, local and global
+  float lsum_dy[32], lsum_dy_xmu[32];
+  float sum_dy[32], sum_dy_xmu[32];
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// Spin until *flag >= want; gives up after ~4 s and raises the error word so a dead peer
+// cannot hang the GPU forever.
+__device__ __forceinline__ void wait_flag(const unsigned long long* flag, unsigned long long want, int* err) {
+  long long t0 = clock64();
+  while (ld_acquire_sys(flag) < want) {
+    if (clock64() - t0 > 8000000000LL) {
+      atomicExch(err, 1);
+      break;
+    }
+  }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// true in exactly one CTA of the grid: the last one to get here.  Resets the ticket so
+// the same counter works on the next launch / graph replay.
+__device__ __forceinline__ bool last_cta_done(unsigned int* ticket, unsigned int n_ctas) {
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    unsigned int t = atomicAdd(ticket, 1u);
+    s_last = (t == n_ctas - 1);
+    if (s_last) *ticket = 0;
+  }
+  __syncthreads();
+  if (s_last) __threadfence();
+  return s_last != 0;
+}
+
+}  // namespace dstep

@@ -1,0 +1,531 @@
+// Forward kernels of the ConvNet step (direct, CUDA-core path; any batch size).
+//   conv1 5x5 p2 (1->16)  + per-channel BN statistics in the epilogue     ddp_main.py:17-18
+//   BN apply + ReLU + MaxPool2                                            ddp_main.py:18-20,24-26
+//   conv2 5x5 p2 (16->32) + BN statistics (also: its data-gradient form)  ddp_main.py:23
+//   Linear(1568,10) + CrossEntropyLoss + its backward, fused               ddp_main.py:28,89,91
+#pragma once
+#include "common.cuh"
+
+namespace dstep {
+
+template <typename T> __device__ __forceinline__ void store4(T* p, float a, float b, float c, float d);
+template <> __device__ __forceinline__ void store4<float>(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+template <> __device__ __forceinline__ void store4<__half>(__half* p, float a, float b, float c, float d) {
+  __half2 lo = __floats2half2_rn(a, b), hi = __floats2half2_rn(c, d);
+  uint2 u;
+  u.x = *reinterpret_cast<unsigned int*>(&lo);
+  u.y = *reinterpret_cast<unsigned int*>(&hi);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+template <> __device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, float a, float b, float c, float d) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+  uint2 u;
+  u.x = *reinterpret_cast<unsigned int*>(&lo);
+  u.y = *reinterpret_cast<unsigned int*>(&hi);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+template <typename T> __device__ __forceinline__ void load2(const T* p, float& a, float& b);
+template <> __device__ __forceinline__ void load2<float>(const float* p, float& a, float& b) {
+  float2 v = *reinterpret_cast<const float2*>(p);
+  a = v.x; b = v.y;
+}
+template <> __device__ __forceinline__ void load2<__half>(const __half* p, float& a, float& b) {
+  float2 v = __half22float2(*reinterpret_cast<const __half2*>(p));
+  a = v.x; b = v.y;
+}
+template <> __device__ __forceinline__ void load2<__nv_bfloat16>(const __nv_bfloat16* p, float& a, float& b) {
+  float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  a = v.x; b = v.y;
+}
+template <typename T> __device__ __forceinline__ void store2(T* p, float a, float b);
+template <> __device__ __forceinline__ void store2<float>(float* p, float a, float b) {
+  *reinterpret_cast<float2*>(p) = make_float2(a, b);
+}
+template <> __device__ __forceinline__ void store2<__half>(__half* p, float a, float b) {
+  *reinterpret_cast<__half2*>(p) = __floats2half2_rn(a, b);
+}
+template <> __device__ __forceinline__ void store2<__nv_bfloat16>(__nv_bfloat16* p, float a, float b) {
+  *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b);
+}
+
+// ---------------------------------------------------------------------------------------
+// Local BN statistics from per-CTA (sum, sum of squares) partials; run by the last CTA of a
+// conv kernel.  `batch_norm_stats` (torch/nn/modules/_functions.py:39).  With SyncBN the
+// (mean, invstd, count) triple is pushed to every rank (the all_gather of _functions.py:74).
+template <int C>
+__device__ void finalize_fwd_stats(const float* part, int rows, float count, float eps, BnStat* st, int layer,
+                                   const CommDev& comm, DevState* ds, int sync) {
+  const int c = threadIdx.x;
+  const bool xchg = sync && comm.world > 1;
+  if (c < C) {
+    double s = 0.0, ss = 0.0;
+    for (int r = 0; r < rows; ++r) {
+      s += (double)__ldcg(&part[(r * C + c) * 2]);
+      ss += (double)__ldcg(&part[(r * C + c) * 2 + 1]);
+    }
+    double mean = s / (double)count;
+    double var = ss / (double)count - mean * mean;
+    if (var < 0.0) var = 0.0;
+    float invstd = (float)(1.0 / sqrt(var + (double)eps));
+    st->lmean[c] = (float)mean;
+    st->linvstd[c] = invstd;
+    st->lvar_unbiased[c] = (float)(var * ((double)count / ((double)count - 1.0)));
+    if (xchg) {
+      for (int q = 0; q < comm.world; ++q) {
+        float* slot = comm.peer[q]->slot_bn_fwd[layer][comm.rank];
+        slot[c] = (float)mean;
+        slot[C + c] = invstd;
+        if (c == 0) slot[2 * C] = count;
+      }
+    }
+  }
+  if (xchg) {
+    __threadfence_system();
+    __syncthreads();
+    if (c < comm.world) st_release_sys(&comm.peer[c]->flag_bn[layer][comm.rank], ds->epoch + 1ull);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// conv1: x fp32 [B,1,28,28] -> y1 T [B,16,28,28].  CTA = 2 channel groups x 98 tiles of
+// 2x4 pixels, one image at a time (grid-stride over images).  K = 25 makes this a
+// bandwidth kernel: the image is staged once in shared memory, every output is written once
+// with 8/16-byte stores, the BN reduction rides in the epilogue.
+struct Conv1Args {
+  const float* x;
+  const float* params;
+  void* y1;
+  float* part;  // [gridDim.x][16][2]
+  BnStat* st;
+  DevState* ds;
+  CommDev comm;
+  int B, dbl, sync;
+  float eps;
+};
+
+constexpr int C1_XS = 36;  // padded row stride of the staged image
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_conv1_fwd(Conv1Args a) {
+  __shared__ __align__(16) float xs[32 * C1_XS];
+  __shared__ __align__(16) float ws[25 * 16];
+  __shared__ float bs[16];
+  __shared__ float red[8][16];
+  const int tid = threadIdx.x;
+  T* __restrict__ y1 = reinterpret_cast<T*>(a.y1);
+
+  for (int i = tid; i < 32 * C1_XS; i += 256) xs[i] = 0.f;
+  for (int i = tid; i < 400; i += 256) {  // ws[k][co] <- rnd(W1[co][k])
+    int co = i / 25, k = i % 25;
+    ws[k * 16 + co] = rnd<T>(a.params[OFF_W1 + i]);
+  }
+  if (tid < 16) bs[tid] = rnd<T>(a.params[OFF_B1 + tid]);
+
+  const int cg = tid >> 7, tile = tid & 127;
+  const bool active = tile < 98;
+  const int tr = tile / 7, tc = tile % 7;
+  float s[8], ss[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = ss[j] = 0.f;
+
+  for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
+    __syncthreads();
+    for (int i = tid; i < 784; i += 256) {
+      int r = i / 28, c = i % 28;
+      xs[(r + 2) * C1_XS + c + 2] = rnd<T>(a.x[(size_t)n * 784 + i]);
+    }
+    __syncthreads();
+    if (!active) continue;
+    float in[6][8];
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      const float4 u = *reinterpret_cast<const float4*>(&xs[(2 * tr + r) * C1_XS + 4 * tc]);
+      const float4 v = *reinterpret_cast<const float4*>(&xs[(2 * tr + r) * C1_XS + 4 * tc + 4]);
+      in[r][0] = u.x; in[r][1] = u.y; in[r][2] = u.z; in[r][3] = u.w;
+      in[r][4] = v.x; in[r][5] = v.y; in[r][6] = v.z; in[r][7] = v.w;
+    }
+    float acc[2][4][8];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[r][c][j] = 0.f;
+#pragma unroll
+    for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 5; ++kw) {
+        const float4 w0 = *reinterpret_cast<const float4*>(&ws[(kh * 5 + kw) * 16 + cg * 8]);
+        const float4 w1 = *reinterpret_cast<const float4*>(&ws[(kh * 5 + kw) * 16 + cg * 8 + 4]);
+        const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+        for (int r = 0; r < 2; ++r)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const float v = in[r + kh][c + kw];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[r][c][j] = fmaf(v, w[j], acc[r][c][j]);
+          }
+      }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int ch = cg * 8 + j;
+      const float b = bs[ch];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        float v[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          v[c] = conv_out<T>(acc[r][c][j], b, a.dbl);
+          s[j] += v[c];
+          ss[j] = fmaf(v[c], v[c], ss[j]);
+        }
+        store4<T>(&y1[(((size_t)n * 16 + ch) * 28 + 2 * tr + r) * 28 + 4 * tc], v[0], v[1], v[2], v[3]);
+      }
+    }
+  }
+  if (a.part == nullptr) return;  // eval: running statistics are used, none are gathered
+  // CTA reduction of the statistics: warps are channel-group pure (4 warps per group)
+  __syncthreads();
+  const int warp = tid >> 5, lane = tid & 31;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float v = warp_sum(s[j]), q = warp_sum(ss[j]);
+    if (lane == 0) { red[warp][j] = v; red[warp][8 + j] = q; }
+  }
+  __syncthreads();
+  if (tid < 32) {  // tid = stat*16 + ch
+    const int stat = tid >> 4, ch = tid & 15, g = ch >> 3, j = ch & 7;
+    float v = 0.f;
+    for (int w = 0; w < 4; ++w) v += red[g * 4 + w][stat * 8 + j];
+    a.part[((size_t)blockIdx.x * 16 + ch) * 2 + stat] = v;
+  }
+  if (last_cta_done(&a.ds->ticket[0], gridDim.x))
+    finalize_fwd_stats<16>(a.part, gridDim.x, (float)a.B * 784.f, a.eps, a.st, 0, a.comm, a.ds, a.sync);
+}
+
+// ---------------------------------------------------------------------------------------
+// BN apply + ReLU + MaxPool 2x2.  Every CTA first obtains the statistics to normalise with:
+// train/W=1: this rank's; train/SyncBN: Chan-merge of all ranks' (mean, invstd, count) in rank
+// order (`batch_norm_gather_stats_with_counts`, _functions.py:106); eval: running buffers.
+// CTA 0 also performs the running-statistics update and num_batches_tracked += 1.
+struct BnPoolArgs {
+  const void* y;
+  void* p;
+  const float* params;
+  BnStat* st;
+  float* bnbuf;
+  long long* nbt;
+  DevState* ds;
+  CommDev comm;
+  int B, layer, eval, sync;
+  float momentum, eps;
+};
+
+template <int C>
+__device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_invstd, int rm_off, int rv_off,
+                                 float local_count) {
+  const int c = threadIdx.x;
+  const bool xchg = !a.eval && a.sync && a.comm.world > 1;
+  if (xchg) {
+    if (c < a.comm.world) wait_flag(&a.comm.self->flag_bn[a.layer][c], a.ds->epoch + 1ull, &a.ds->error);
+    __syncthreads();
+  }
+  if (c < C) {
+    float mean, invstd, var_unb, n_total = local_count;
+    if (a.eval) {
+      mean = a.bnbuf[rm_off + c];
+      invstd = 1.0f / sqrtf(a.bnbuf[rv_off + c] + a.eps);
+      var_unb = 0.f;
+    } else if (xchg) {
+      float m = 0.f, m2 = 0.f, n = 0.f;
+      for (int r = 0; r < a.comm.world; ++r) {
+        const float* slot = a.comm.self->slot_bn_fwd[a.layer][r];
+        const float mu_r = __ldcg(&slot[c]), is_r = __ldcg(&slot[C + c]), n_r = __ldcg(&slot[2 * C]);
+        const float v = (1.0f / (is_r * is_r) - a.eps) * n_r;
+        const float f = 1.0f / (n + n_r);
+        const float d = m - mu_r;
+        m2 = m2 + v + d * d * n * n_r * f;
+        m = n * f * m + n_r * f * mu_r;
+        n += n_r;
+      }
+      mean = m;
+      invstd = 1.0f / sqrtf(m2 / n + a.eps);
+      var_unb = m2 / (n - 1.0f);
+      n_total = n;
+    } else {
+      mean = a.st->lmean[c];
+      invstd = a.st->linvstd[c];
+      var_unb = a.st->lvar_unbiased[c];
+    }
+    s_mean[c] = mean;
+    s_invstd[c] = invstd;
+    if (blockIdx.x == 0 && !a.eval) {
+      a.st->mean[c] = mean;
+      a.st->invstd[c] = invstd;
+      if (c == 0) {
+        a.st->n_total = n_total;
+        a.nbt[a.layer] += 1;
+      }
+      a.bnbuf[rm_off + c] = (1.0f - a.momentum) * a.bnbuf[rm_off + c] + a.momentum * mean;
+      a.bnbuf[rv_off + c] = (1.0f - a.momentum) * a.bnbuf[rv_off + c] + a.momentum * var_unb;
+    }
+  }
+  __syncthreads();
+}
+
+template <typename T, int C, int H>
+__global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
+  constexpr int HP = H / 2;
+  constexpr int OFF_G = (C == 16) ? OFF_G1 : OFF_G2, OFF_BE = (C == 16) ? OFF_BE1 : OFF_BE2;
+  constexpr int RM = (C == 16) ? BNB_RM1 : BNB_RM2, RV = (C == 16) ? BNB_RV1 : BNB_RV2;
+  __shared__ float s_mean[C], s_invstd[C], s_g[C], s_b[C];
+  if (threadIdx.x < C) {
+    s_g[threadIdx.x] = a.params[OFF_G + threadIdx.x];
+    s_b[threadIdx.x] = a.params[OFF_BE + threadIdx.x];
+  }
+  bn_forward_stats<C>(a, s_mean, s_invstd, RM, RV, (float)a.B * (float)(H * H));
+  const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
+  T* __restrict__ p = reinterpret_cast<T*>(a.p);
+  const size_t total = (size_t)a.B * C * HP * HP;
+  for (size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (size_t)gridDim.x * 256) {
+    const int pw = (int)(idx % HP), ph = (int)((idx / HP) % HP);
+    const size_t plane = idx / (HP * HP);
+    const int c = (int)(plane % C);
+    const T* src = y + (plane * H + 2 * ph) * H + 2 * pw;
+    float v0, v1, v2, v3;
+    load2<T>(src, v0, v1);
+    load2<T>(src + H, v2, v3);
+    const float mu = s_mean[c], is = s_invstd[c], g = s_g[c], b = s_b[c];
+    v0 = rnd<T>((v0 - mu) * is * g + b);
+    v1 = rnd<T>((v1 - mu) * is * g + b);
+    v2 = rnd<T>((v2 - mu) * is * g + b);
+    v3 = rnd<T>((v3 - mu) * is * g + b);
+    const float m = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
+    stf<T>(&p[idx], m);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// 5x5 pad-2 convolution on 14x14 planes, direct form.  MODE 0: conv2 forward (16->32, bias,
+// BN statistics).  MODE 2: conv2 data gradient (32->16): the same correlation with the kernel
+// flipped and the channel roles swapped.  CTA = one image x 8 output channels; thread = one
+// output channel x 2 rows x 7 columns.
+struct Conv14Args {
+  const void* in;
+  const float* params;
+  void* out;
+  float* part;  // MODE 0: [gridDim.x][32][2]
+  BnStat* st;
+  DevState* ds;
+  CommDev comm;
+  int B, dbl, sync;
+  float eps;
+};
+
+constexpr int C14_RS = 20;  // padded row stride (18 used)
+
+template <typename T, int CI, int CO, int MODE>
+__global__ void __launch_bounds__(128) k_conv14(Conv14Args a) {
+  extern __shared__ __align__(16) float smem[];
+  float* in_s = smem;                      // [CI][18][C14_RS]
+  float* w_s = smem + CI * 18 * C14_RS;    // [8][CI][25]
+  __shared__ float red[112][2];
+  const int tid = threadIdx.x;
+  const int cog = blockIdx.y;
+  const T* __restrict__ in = reinterpret_cast<const T*>(a.in);
+  T* __restrict__ out = reinterpret_cast<T*>(a.out);
+
+  for (int i = tid; i < CI * 18 * C14_RS; i += 128) in_s[i] = 0.f;
+  for (int i = tid; i < 8 * CI * 25; i += 128) {
+    const int k = i % 25, ci = (i / 25) % CI, col = i / (25 * CI);
+    float w;
+    if (MODE == 0) {
+      w = a.params[OFF_W2 + ((cog * 8 + col) * CI + ci) * 25 + k];
+    } else {  // out channel (cog*8+col) is conv2's input channel; ci runs over conv2's outputs
+      w = a.params[OFF_W2 + (ci * 16 + cog * 8 + col) * 25 + (24 - k)];
+    }
+    w_s[i] = rnd<T>(w);
+  }
+  const int col = tid / 14, t = tid % 14;
+  const bool active = tid < 112;
+  const int rp = t >> 1, c0 = (t & 1) * 7;
+  const int co = cog * 8 + col;
+  const float bias = (MODE == 0 && active) ? rnd<T>(a.params[OFF_B2 + co]) : 0.f;
+  float s = 0.f, ss = 0.f;
+
+  for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
+    __syncthreads();
+    for (int i = tid; i < CI * 196; i += 128) {
+      const int ci = i / 196, r = (i % 196) / 14, c = i % 14;
+      in_s[(ci * 18 + r + 2) * C14_RS + c + 2] = ldf<T>(&in[(size_t)n * CI * 196 + i]);
+    }
+    __syncthreads();
+    if (!active) continue;
+    float acc[2][7];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int c = 0; c < 7; ++c) acc[r][c] = 0.f;
+    const float* wt = w_s + col * CI * 25;
+#pragma unroll 2
+    for (int ci = 0; ci < CI; ++ci) {
+      const float* base = in_s + (ci * 18 + 2 * rp) * C14_RS + c0;
+#pragma unroll
+      for (int ri = 0; ri < 6; ++ri) {
+        float row[11];
+#pragma unroll
+        for (int c = 0; c < 11; ++c) row[c] = base[ri * C14_RS + c];
+#pragma unroll
+        for (int orow = 0; orow < 2; ++orow) {
+          const int kh = ri - orow;
+          if (kh >= 0 && kh < 5) {
+#pragma unroll
+            for (int kw = 0; kw < 5; ++kw) {
+              const float w = wt[ci * 25 + kh * 5 + kw];
+#pragma unroll
+              for (int px = 0; px < 7; ++px) acc[orow][px] = fmaf(row[px + kw], w, acc[orow][px]);
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int c = 0; c < 7; ++c) {
+        float v;
+        if (MODE == 0) {
+          v = conv_out<T>(acc[r][c], bias, a.dbl);
+          s += v;
+          ss = fmaf(v, v, ss);
+        } else {
+          v = acc[r][c];
+        }
+        stf<T>(&out[(((size_t)n * CO + co) * 14 + 2 * rp + r) * 14 + c0 + c], v);
+      }
+  }
+  if (MODE == 0 && a.part != nullptr) {
+    __syncthreads();
+    if (active) { red[tid][0] = s; red[tid][1] = ss; }
+    __syncthreads();
+    if (tid < 16) {
+      const int cl = tid >> 1, stat = tid & 1;
+      float v = 0.f;
+      for (int i = 0; i < 14; ++i) v += red[cl * 14 + i][stat];
+      a.part[((size_t)blockIdx.x * 32 + cog * 8 + cl) * 2 + stat] = v;
+    }
+    if (last_cta_done(&a.ds->ticket[1], gridDim.x * gridDim.y))
+      finalize_fwd_stats<32>(a.part, gridDim.x, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Linear(1568 -> 10) + CrossEntropyLoss (+ the backward of both up to d(pool2 out)).
+// CTA = 7 warps, one image at a time; every thread keeps its 7x10 slice of the (rounded)
+// fc weight in registers across images.  N = 10 is far too narrow for an MMA tile.
+struct FcArgs {
+  const void* p2;        // [B,1568]
+  const float* params;
+  const long long* y;    // labels (may be null in eval)
+  void* logits;          // [B,10] T
+  void* dlogits;         // [B,10] T          (train)
+  void* dflat;           // [B,1568] T        (train)  d(pool2 out)
+  float* nll;            // [B]               (train)
+  float* counts;         // [2] correct,size  (eval)
+  const DevState* ds;
+  int B, use_scaler, eval;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
+  __shared__ float red[7][10];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const T* __restrict__ p2 = reinterpret_cast<const T*>(a.p2);
+  T* __restrict__ logits = reinterpret_cast<T*>(a.logits);
+  float w[10][7];
+#pragma unroll
+  for (int j = 0; j < 10; ++j)
+#pragma unroll
+    for (int i = 0; i < 7; ++i) w[j][i] = rnd<T>(a.params[OFF_WFC + j * 1568 + tid + 224 * i]);
+  float b[10];
+#pragma unroll
+  for (int j = 0; j < 10; ++j) b[j] = rnd<T>(a.params[OFF_BFC + j]);
+  // incoming gradient of the loss: `scale` cast to the loss dtype (65536 -> inf in fp16)
+  const float gl = a.use_scaler ? rnd<T>(a.ds->scale) : 1.0f;
+  const float g = rnd<T>(-(gl / (float)a.B));
+
+  for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
+    float xk[7];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) xk[i] = ldf<T>(&p2[(size_t)n * 1568 + tid + 224 * i]);
+#pragma unroll
+    for (int j = 0; j < 10; ++j) {
+      float acc = 0.f;
+#pragma unroll
+      for (int i = 0; i < 7; ++i) acc = fmaf(xk[i], w[j][i], acc);
+      acc = warp_sum(acc);
+      if (lane == 0) red[warp][j] = acc;
+    }
+    __syncthreads();
+    float lg[10], mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 10; ++j) {
+      float v = 0.f;
+#pragma unroll
+      for (int q = 0; q < 7; ++q) v += red[q][j];
+      lg[j] = rnd<T>(v + b[j]);
+      mx = fmaxf(mx, lg[j]);
+    }
+    if (a.eval) {
+#pragma unroll
+      for (int j = 0; j < 10; ++j)
+        if (tid == j) stf<T>(&logits[(size_t)n * 10 + j], lg[j]);
+      if (tid == 0 && a.y != nullptr) {
+        // argmax: first maximum, NaN counts as the maximum
+        float best = lg[0];
+        int arg = 0;
+#pragma unroll
+        for (int j = 1; j < 10; ++j)
+          if (lg[j] > best || (lg[j] != lg[j] && best == best)) { best = lg[j]; arg = j; }
+        if ((long long)arg == a.y[n]) atomicAdd(&a.counts[0], 1.0f);
+        atomicAdd(&a.counts[1], 1.0f);
+      }
+      __syncthreads();
+      continue;
+    }
+    float se = 0.f;
+#pragma unroll
+    for (int j = 0; j < 10; ++j) se += expf(lg[j] - mx);
+    const float lse = logf(se);
+    const int label = (int)a.y[n];
+    float dl[10], nll = 0.f;
+#pragma unroll
+    for (int j = 0; j < 10; ++j) {
+      const float lsm = rnd<T>(lg[j] - mx - lse);
+      if (j == label) nll = -lsm;
+      dl[j] = rnd<T>((j == label ? g : 0.f) - expf(lsm) * g);
+    }
+#pragma unroll
+    for (int j = 0; j < 10; ++j)
+      if (tid == j) {
+        stf<T>(&logits[(size_t)n * 10 + j], lg[j]);
+        stf<T>(&reinterpret_cast<T*>(a.dlogits)[(size_t)n * 10 + j], dl[j]);
+      }
+    if (tid == 0) a.nll[n] = nll;
+    T* __restrict__ dflat = reinterpret_cast<T*>(a.dflat);
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 10; ++j) acc = fmaf(dl[j], w[j][i], acc);
+      stf<T>(&dflat[(size_t)n * 1568 + tid + 224 * i], acc);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace dstep

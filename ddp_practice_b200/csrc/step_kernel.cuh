@@ -1,0 +1,215 @@
+// The DDP Reducer + GradScaler + SGD tail of the step, as ONE launch of one 8-CTA cluster:
+//   * finish the weight-gradient partial sums, round to the autocast dtype (autocast keeps
+//     conv/linear weight gradients in that dtype: autocast_mode.h:824,840)
+//   * Reducer: bucket = grad * (1/W), all-reduce SUM        reducer.hpp:276, ddp_main.py:121
+//       -> one-shot push over NVLink peer memory into every rank's inbox, per-chunk flags,
+//          summed in fixed rank order so every replica gets identical bits
+//   * GradScaler.unscale_: grad *= float(1/double(scale)), found_inf    grad_scaler.py:351-356
+//   * GradScaler.step: SGD p += (-lr) * g unless found_inf             grad_scaler.py:371, sgd.py:473
+//   * GradScaler.update: `_amp_update_scale_`                           grad_scaler.py:549-556
+//   * DDP's rank-0 broadcast of the BN running buffers (plain-BN DDP)   distributed.py:2243-2257
+//   * loss = mean(nll) in the loss dtype                                ddp_main.py:89
+// 8 x 1024 threads x 4 floats cover the 29,034-element bucket, so every gradient element
+// stays in registers from the partial sums to the parameter update; the only grid-wide
+// dependency (found_inf) is resolved through distributed shared memory.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+
+namespace dstep {
+namespace cg = cooperative_groups;
+
+struct StepArgs {
+  float* params;
+  float* grads;         // tap T-c
+  float* grads_scaled;  // tap T-b
+  const float* gpart;   // [rows][N_PAD]
+  const float* gdirect; // [N_PAD]
+  const float* nll;     // [B]
+  float* bnbuf;
+  long long* nbt;
+  DevState* ds;
+  CommDev comm;
+  int B;
+  int rows_conv1, rows_conv2w, rows_conv2b, rows_fc;
+  int use_scaler, sync;
+  float lr, growth_factor, backoff_factor;
+  int growth_interval;
+};
+
+template <typename T>
+__global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS) k_step(StepArgs a) {
+  cg::cluster_group cluster = cg::this_cluster();
+  __shared__ int s_nonfinite;
+  const int tid = threadIdx.x, cta = blockIdx.x;
+  const int e = (cta * STEP_THREADS + tid) * 4;
+  const bool valid = e < N_PARAM;  // last float4 (29032..29035) is half padding
+  const int W = a.comm.world, rank = a.comm.rank;
+  const unsigned long long epoch = a.ds->epoch;
+  const float scale = a.ds->scale;
+  if (tid == 0) s_nonfinite = 0;
+  __syncthreads();
+
+  // ---- 1. finish the local gradient (fixed row order => deterministic)
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (valid) {
+    int rows;
+    bool round_t = true;
+    if (e < OFF_G1) rows = a.rows_conv1;
+    else if (e < OFF_W2) { rows = 0; round_t = false; }
+    else if (e < OFF_B2) rows = a.rows_conv2w;
+    else if (e < OFF_G2) rows = a.rows_conv2b;
+    else if (e < OFF_WFC) { rows = 0; round_t = false; }
+    else rows = a.rows_fc;
+    if (round_t) {
+      const float* p = a.gpart + e;
+#pragma unroll 4
+      for (int r = 0; r < rows; ++r) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(p + (size_t)r * N_PAD));
+        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+      }
+      g.x = rnd<T>(g.x); g.y = rnd<T>(g.y); g.z = rnd<T>(g.z); g.w = rnd<T>(g.w);
+    } else {
+      g = __ldcg(reinterpret_cast<const float4*>(a.gdirect + e));
+    }
+    if (e + 4 > N_PARAM) { g.z = 0.f; g.w = 0.f; }
+  }
+
+  // ---- 2. DDP all-reduce: pre-divide, push to every peer's inbox, flag, wait, sum in rank order
+  const float inv_w = 1.0f / (float)W;
+  float4 h = make_float4(g.x * inv_w, g.y * inv_w, g.z * inv_w, g.w * inv_w);
+  float4 tot = h;
+  if (W > 1) {
+    const int par = (int)(epoch & 1ull);
+    if (valid) {
+      for (int q = 0; q < W; ++q)
+        if (q != rank) *reinterpret_cast<float4*>(&a.comm.peer[q]->inbox[par][rank][e]) = h;
+    }
+    if (!a.sync && rank == 0 && cta == 0) {  // plain-BN DDP: rank 0's buffers win
+      for (int q = 1; q < W; ++q) {
+        if (tid < N_BNBUF) a.comm.peer[q]->slot_bnbuf[tid] = a.bnbuf[tid];
+        if (tid < 2) a.comm.peer[q]->slot_nbt[tid] = a.nbt[tid];
+      }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid < W && tid != rank) st_release_sys(&a.comm.peer[tid]->flag_grad[rank][cta], epoch + 1ull);
+    if (tid < W && tid != rank) wait_flag(&a.comm.self->flag_grad[tid][cta], epoch + 1ull, &a.ds->error);
+    __syncthreads();
+    if (valid) {
+      tot = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int q = 0; q < W; ++q) {
+        const float4 v = (q == rank) ? h : __ldcg(reinterpret_cast<const float4*>(&a.comm.self->inbox[par][q][e]));
+        tot.x += v.x; tot.y += v.y; tot.z += v.z; tot.w += v.w;
+      }
+    }
+    if (!a.sync && rank != 0 && cta == 0) {
+      if (tid < N_BNBUF) a.bnbuf[tid] = __ldcg(&a.comm.self->slot_bnbuf[tid]);
+      if (tid < 2) a.nbt[tid] = a.comm.self->slot_nbt[tid];
+    }
+  }
+
+  // ---- 3. unscale + non-finite check (every element is multiplied, finite or not)
+  float4 u = tot;
+  if (a.use_scaler) {
+    const float inv_scale = (float)(1.0 / (double)scale);
+    u = make_float4(tot.x * inv_scale, tot.y * inv_scale, tot.z * inv_scale, tot.w * inv_scale);
+    const bool bad = !(isfinite(u.x) && isfinite(u.y) && isfinite(u.z) && isfinite(u.w));
+    if (valid && bad) atomicOr(&s_nonfinite, 1);
+  }
+  if (valid) {
+    if (e + 4 <= N_PARAM) {
+      *reinterpret_cast<float4*>(a.grads_scaled + e) = tot;
+      *reinterpret_cast<float4*>(a.grads + e) = u;
+    } else {
+      a.grads_scaled[e] = tot.x; a.grads_scaled[e + 1] = tot.y;
+      a.grads[e] = u.x; a.grads[e + 1] = u.y;
+    }
+  }
+
+  // ---- 4. cluster-wide found_inf through distributed shared memory
+  cluster.sync();
+  int found = 0;
+#pragma unroll
+  for (int r = 0; r < STEP_CTAS; ++r) found |= *cluster.map_shared_rank(&s_nonfinite, r);
+  cluster.sync();  // nobody may exit (and release its smem) before every CTA has read it
+
+  // ---- 5. SGD (skipped on overflow), same expression as _foreach_add_(p, g, alpha=-lr)
+  if (valid && !found) {
+    if (e + 4 <= N_PARAM) {
+      float4 p = *reinterpret_cast<const float4*>(a.params + e);
+      p.x = fmaf(-a.lr, u.x, p.x); p.y = fmaf(-a.lr, u.y, p.y);
+      p.z = fmaf(-a.lr, u.z, p.z); p.w = fmaf(-a.lr, u.w, p.w);
+      *reinterpret_cast<float4*>(a.params + e) = p;
+    } else {
+      a.params[e] = fmaf(-a.lr, u.x, a.params[e]);
+      a.params[e + 1] = fmaf(-a.lr, u.y, a.params[e + 1]);
+    }
+  }
+
+  // ---- 6. scalar state: loss, scale, tracker, epoch
+  if (cta == 0 && tid < 32) {
+    float s = 0.f;
+    for (int i = tid; i < a.B; i += 32) s += a.nll[i];
+    s = warp_sum(s);
+    if (tid == 0) {
+      a.ds->loss = rnd<T>(s / (float)a.B);
+      a.ds->found_inf = found ? 1.0f : 0.0f;
+      if (a.use_scaler) {
+        if (found) {
+          a.ds->scale = scale * a.backoff_factor;
+          a.ds->growth_tracker = 0;
+        } else {
+          const int t = a.ds->growth_tracker + 1;
+          if (t == a.growth_interval) {
+            const float grown = scale * a.growth_factor;
+            if (isfinite(grown)) a.ds->scale = grown;
+            a.ds->growth_tracker = 0;
+          } else {
+            a.ds->growth_tracker = t;
+          }
+        }
+      }
+      a.ds->epoch = epoch + 1ull;
+    }
+  }
+}
+
+// dist.reduce(size, 0, SUM); dist.reduce(correct, 0, SUM)  (ddp_main.py:108-109): every
+// rank pushes its two fp32 counters into rank 0's slots; rank 0 sums them in rank order.
+struct CountsArgs {
+  float* counts;
+  DevState* ds;
+  CommDev comm;
+};
+
+__global__ void k_reduce_counts(CountsArgs a) {
+  const int tid = threadIdx.x, W = a.comm.world, rank = a.comm.rank;
+  const unsigned long long ep = a.ds->eval_epoch;
+  if (W > 1) {
+    if (tid == 0) {
+      // the slot is single-buffered: rank 0 must have consumed our previous push
+      if (ep > 0) wait_flag(&a.comm.self->flag_counts_ack, ep, &a.ds->error);
+      a.comm.peer[0]->slot_counts[rank][0] = a.counts[0];
+      a.comm.peer[0]->slot_counts[rank][1] = a.counts[1];
+      __threadfence_system();
+      st_release_sys(&a.comm.peer[0]->flag_counts[rank], ep + 1ull);
+    }
+    if (rank == 0) {
+      if (tid < W) wait_flag(&a.comm.self->flag_counts[tid], ep + 1ull, &a.ds->error);
+      __syncthreads();
+      if (tid < 2) {
+        float s = 0.f;
+        for (int r = 0; r < W; ++r) s += __ldcg(&a.comm.self->slot_counts[r][tid]);
+        a.counts[tid] = s;
+      }
+      __syncthreads();
+      if (tid < W) st_release_sys(&a.comm.peer[tid]->flag_counts_ack, ep + 1ull);
+    }
+  }
+  __syncthreads();
+  if (tid == 0) a.ds->eval_epoch = ep + 1ull;
+}
+
+}  // namespace dstep

@@ -1,0 +1,142 @@
+/*
+ * ddpstep.h -- C ABI of the B200-native fused DDP + AMP ConvNet training step.
+ *
+ * The reference (gbbin/DDP-practice) has no FFI of its own: its "operator API" is the
+ * PyTorch object surface touched by ddp_main.py.  Every entry point below therefore
+ * cites the reference call (file:line) whose work it performs.  The Python mirror of
+ * that surface (ddp_practice_b200/shim.py) binds these symbols with ctypes; see
+ * INTEGRATION.md for the binding a maintainer of the reference would add.
+ *
+ * Conventions: plain C types only; every function returns 0 on success or a negative
+ * DDPSTEP_E_* code (ddpstep_last_error() gives the text); one host thread per context
+ * (process-per-GPU, ddp_main.py:176); all device memory is owned by the library; the
+ * caller supplies the CUDA stream as a void* (cudaStream_t), NULL = default stream.
+ */
+#ifndef DDPSTEP_H
+#define DDPSTEP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDPSTEP_ABI_VERSION 1
+
+#define DDPSTEP_N_PARAMS 29034   /* flat fp32 parameter / gradient bucket length   */
+#define DDPSTEP_N_BNBUF 96       /* rm1[16] rv1[16] rm2[32] rv2[32]                */
+#define DDPSTEP_HANDLE_BYTES 64  /* sizeof(cudaIpcMemHandle_t)                     */
+#define DDPSTEP_MAX_WORLD 8
+
+enum { DDPSTEP_FP32 = 0, DDPSTEP_FP16 = 1, DDPSTEP_BF16 = 2 };
+
+enum {
+  DDPSTEP_OK = 0,
+  DDPSTEP_E_ARG = -1,      /* bad argument (batch > batch_cap, world > 8, null pointer ...) */
+  DDPSTEP_E_CUDA = -2,     /* a CUDA runtime call failed                                    */
+  DDPSTEP_E_STATE = -3,    /* call out of order (e.g. step before peers were imported)      */
+  DDPSTEP_E_PEER = -4,     /* a peer did not answer within the spin timeout                 */
+  DDPSTEP_E_ARCH = -5      /* device is not sm_100                                          */
+};
+
+typedef struct ddpstep_ctx ddpstep_ctx;
+
+typedef struct ddpstep_config {
+  int32_t abi_version;     /* DDPSTEP_ABI_VERSION                                            */
+  int32_t rank, world;     /* dist.get_rank() / WORLD_SIZE                 ddp_main.py:65,72 */
+  int32_t device;          /* CUDA device ordinal = local_rank             ddp_main.py:71    */
+  int32_t dtype;           /* autocast dtype: DDPSTEP_FP16 = `autocast()`  ddp_main.py:31;
+                              DDPSTEP_FP32 = origin_main.py (no autocast)                    */
+  int32_t batch_cap;       /* largest per-rank batch ever passed (-b)      ddp_main.py:51    */
+  int32_t use_scaler;      /* 1 = GradScaler path (ddp_main.py:91-93), 0 = origin_main.py:64 */
+  int32_t sync_bn;         /* 1 = SyncBatchNorm statistics over all ranks  ddp_main.py:120   */
+  int32_t use_graph;       /* 1 = replay the step as one captured CUDA graph                 */
+  int32_t conv_bias_double_round; /* 1 = round conv output, then add bias and round again
+                              (ATen cuDNN path); 0 = round once                              */
+  float lr;                /* SGD learning rate                            ddp_main.py:125   */
+  float init_scale, growth_factor, backoff_factor; /* GradScaler()  grad_scaler.py:126-128   */
+  int32_t growth_interval; /*                                       grad_scaler.py:129       */
+  float bn_momentum, bn_eps; /* nn.BatchNorm2d defaults             ddp_main.py:18,24        */
+} ddpstep_config;
+
+/* Device pointers into the context's state, for zero-copy views (torch tensors that alias
+ * them back `model.parameters()`, `p.grad`, BN buffers, `scaler._scale`).                    */
+typedef struct ddpstep_ptrs {
+  float* params;           /* [29034] fp32 master weights, definition order  ddp_main.py:16-28 */
+  float* grads;            /* [29034] tap T-c: all-reduced, unscaled grads   ddp_main.py:92    */
+  float* grads_scaled;     /* [29034] tap T-b: all-reduced, still scaled     ddp_main.py:91    */
+  float* bn_buffers;       /* [96] running_mean/var of both BN layers                          */
+  int64_t* num_batches_tracked; /* [2]                                                         */
+  float* scale;            /* [1] GradScaler._scale                          grad_scaler.py:176 */
+  int32_t* growth_tracker; /* [1] GradScaler._growth_tracker                                   */
+  float* found_inf;        /* [1] of the last step (0.0 / 1.0)               grad_scaler.py:371 */
+  float* loss;             /* [1] tap T-a: this rank's loss of the last step ddp_main.py:89    */
+  void* logits;            /* [batch_cap,10] in `dtype`: outputs of the last forward           */
+  float* counts;           /* [2] correct, size accumulators of test()       ddp_main.py:99-107 */
+  float* input_stage;      /* [batch_cap,784] fp32 staging buffer for images                   */
+  int64_t* label_stage;    /* [batch_cap] staging buffer for labels                            */
+} ddpstep_ptrs;
+
+/* Fill a config with the reference's defaults (fp16 autocast, GradScaler(), lr 1e-4). */
+void ddpstep_default_config(ddpstep_config* cfg);
+
+/* ConvNet().cuda() + DDP(...) + SGD + GradScaler() construction: ddp_main.py:117-126.
+ * Allocates all device state for one rank on cfg->device.  Parameters start at zero:
+ * load them with ddpstep_load_state.                                                        */
+int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out);
+/* dist.destroy_process_group() + object teardown: ddp_main.py:170.                          */
+int ddpstep_destroy(ddpstep_ctx* ctx);
+const char* ddpstep_last_error(const ddpstep_ctx* ctx);  /* ctx may be NULL: create() errors */
+
+/* Peer bootstrap, replaces ProcessGroupNCCL communicator setup (init_process_group,
+ * ddp_main.py:73).  export: 64-byte IPC handle of this rank's symmetric region; the caller
+ * all-gathers the handles over its own control plane (the c10d store) and passes the
+ * world*64 bytes, rank-major, to import.  world == 1 needs neither.                         */
+int ddpstep_export_handle(ddpstep_ctx* ctx, void* handle64);
+int ddpstep_import_peers(ddpstep_ctx* ctx, const void* handles, int32_t world);
+
+/* DDP's construction-time broadcast of rank 0's parameters and buffers
+ * (distributed.py:881-890) ends with every rank calling this with the same host arrays.
+ * nbt may be NULL (zeros).                                                                  */
+int ddpstep_load_state(ddpstep_ctx* ctx, const float* params29034, const float* bn_buffers96,
+                       const int64_t* nbt2);
+/* model.state_dict() / scaler.state_dict(): ddp_main.py:165-169.  Any pointer may be NULL.  */
+int ddpstep_read_state(ddpstep_ctx* ctx, float* params29034, float* bn_buffers96, int64_t* nbt2,
+                       float* scale, int32_t* growth_tracker);
+int ddpstep_set_scaler(ddpstep_ctx* ctx, float scale, int32_t growth_tracker);
+int ddpstep_state_ptrs(ddpstep_ctx* ctx, ddpstep_ptrs* out);
+
+/* One iteration of train(): ddp_main.py:86-93 (origin_main.py:60-66 when use_scaler == 0):
+ * forward, CrossEntropyLoss, scale(loss).backward() with the DDP all-reduce, scaler.step
+ * (unscale, inf check, SGD) and scaler.update, as one stream-ordered launch sequence /
+ * graph replay.  x: [batch,1,28,28] fp32, y: [batch] int64, both DEVICE pointers.          */
+int ddpstep_train_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
+                       void* stream);
+/* Same, from HOST buffers (the `.cuda()` copies of ddp_main.py:86-87 included); if loss_out
+ * is not NULL the loss is copied back and the call synchronises the stream.                 */
+int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* x_host, const int64_t* y_host,
+                            int32_t batch, float* loss_out, void* stream);
+
+/* One iteration of test(): ddp_main.py:101-107.  Eval-mode forward (running statistics),
+ * logits left in ptrs.logits; when y_dev != NULL also `size += batch` and
+ * `correct += (argmax == y).sum()` into ptrs.counts.                                        */
+int ddpstep_eval_batch(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
+                       void* stream);
+int ddpstep_reset_counts(ddpstep_ctx* ctx, void* stream);        /* ddp_main.py:99-100       */
+/* dist.reduce(size, 0, SUM); dist.reduce(correct, 0, SUM): ddp_main.py:108-109.  On rank 0
+ * ptrs.counts then holds the sums over all ranks.                                           */
+int ddpstep_reduce_counts(ddpstep_ctx* ctx, void* stream);
+int ddpstep_read_counts(ddpstep_ctx* ctx, float* correct, float* size, void* stream);
+
+/* Test / profiling taps. which: 0 y1, 1 p1, 2 y2, 3 p2 (activations in `dtype`),
+ * 4 dlogits, 5 d(conv2 out), 6 d(pool1 out).  Copies min(bytes, size) to host.             */
+int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* host, int64_t bytes);
+/* Number of kernel launches (graph kernel nodes count one each) issued so far.             */
+int64_t ddpstep_launch_count(const ddpstep_ctx* ctx);
+/* Device-side error word (peer timeout etc.), 0 = healthy.  Synchronises the device.       */
+int ddpstep_device_status(ddpstep_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDPSTEP_H */

@@ -64,3 +64,30 @@ def assert_grads_close(got, ref, tol, what="", metric="l2"):
     errs = grad_errors(got, ref, metric)
     bad = {k: v for k, v in errs.items() if not v <= tol}
     assert not bad, f"{what} gradient mismatch ({metric}, tol {tol}): {bad}"
+
+
+# ---- discrete routing (ReLU mask + max-pool winner) --------------------------------------
+# Two correct implementations that differ in the last ulp of a conv output can disagree on
+# which element of a 2x2 window wins the pool (or whether a ReLU is open) when two values
+# tie at the storage precision.  Each such flip reroutes one whole gradient path (~1/B of a
+# layer's gradient signal), so gradient tolerances are stated for "routing agrees" and
+# relaxed, with the flip count reported, when it does not.
+
+
+def routing_of(a):
+    """a: BN output [B,C,H,W] (fp32 values).  Returns (winner index 0..3, live mask)."""
+    from oracle.convnet_oracle import _relu_pool
+    p, arg = _relu_pool(a)
+    return arg, p > 0
+
+
+def bn_out_from_conv(y, gamma, beta, dtype):
+    """BN(train) output recomputed from a conv output with the oracle's formulas."""
+    from oracle import convnet_oracle as O
+    mean, invstd, _ = O._local_stats(y)
+    return O._bn_apply(y, mean, invstd, gamma, beta, O._DT[dtype])
+
+
+def count_flips(r_a, r_b):
+    (arg_a, live_a), (arg_b, live_b) = r_a, r_b
+    return int(((live_a != live_b) | (live_a & live_b & (arg_a != arg_b))).sum())

@@ -1,0 +1,324 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the
+C ABI (libddpstep.so via ddp_practice_b200.Engine); the checker is the CPU oracle, the
+committed golden vectors, and the reference's own stack (torch CUDA eager) run live."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import convnet_oracle as O
+from tests.helpers import (assert_grads_close, bn_out_from_conv, count_flips, grad_errors, load_golden, routing_of,
+                           state_from_golden)
+from tests.refmodel import RefConvNet, RefTrainer, bn_buffers, flat_params, nbt
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-5  # relative (L2 per parameter tensor), north_star
+AMP_TOL = 2e-2   # relative under fp16 / bf16 autocast, north_star
+# When the two sides disagree on k > 0 ReLU / max-pool routing decisions (ties at the last
+# ulp, see tests/helpers.py) each flip moves a whole gradient path; bounds for those steps:
+FP32_FLIP_TOL = 2e-2
+AMP_FLIP_TOL = 6e-2
+MAX_FLIP_FRACTION = 1e-3  # of all pooling windows
+TDT = {"fp32": None, "fp16": torch.float16, "bf16": torch.bfloat16}
+
+
+def _engine(**kw):
+    from ddp_practice_b200 import Engine
+    return Engine(**kw)
+
+
+def _bn_of(st):
+    return torch.cat([st.running_mean[0], st.running_var[0], st.running_mean[1], st.running_var[1]]).numpy()
+
+
+def _seed_state(seed=3407):
+    torch.manual_seed(seed)
+    m = RefConvNet(None, "cpu")
+    return O.OracleState.from_state_dict(m.state_dict())
+
+
+# ------------------------------------------------------------------ golden vectors of the reference
+
+
+def test_fp32_golden_origin_main():
+    """configs[0]: origin_main.py's fp32 step, against vectors made by the reference itself."""
+    g = load_golden("origin_fp32.npz")
+    B, S = int(g["batch"]), int(g["steps"])
+    e = _engine(dtype="fp32", batch_cap=B, use_scaler=False)
+    e.load_state(g["init_params"], np.concatenate([g["init_rm0"], g["init_rv0"], g["init_rm1"], g["init_rv1"]]))
+    x, y = torch.from_numpy(g["x"]).cuda(), torch.from_numpy(g["y"]).cuda()
+    for s in range(S):
+        e.train_step(x[s * B:(s + 1) * B].contiguous(), y[s * B:(s + 1) * B].contiguous())
+        torch.cuda.synchronize()
+        assert e.loss.item() == pytest.approx(g["losses"][s], rel=FP32_TOL)
+        assert_grads_close(e.grads.cpu(), g["grads"][s], FP32_TOL, f"step {s}")
+    st = e.read_state()
+    fin, ini = g["final_params"], g["init_params"]
+    # (final - init) is a difference of nearly equal fp32 numbers: good to ~1e-3 only
+    assert_grads_close(st["params"] - ini, fin - ini, 2e-3, "sgd update")
+    assert np.allclose(st["params"], fin, rtol=1e-5, atol=1e-7)
+    ref_bn = np.concatenate([g["final_rm0"], g["final_rv0"], g["final_rm1"], g["final_rv1"]])
+    assert np.allclose(st["bn_buffers"], ref_bn, rtol=1e-5, atol=1e-7)
+    assert list(st["nbt"]) == [S, S]
+    e.close()
+
+
+def test_eval_counts_golden():
+    """test() of origin_main.py:69-81 against reference-made logits and counts."""
+    g = load_golden("test_counts.npz")
+    e = _engine(dtype="fp32", batch_cap=32, use_scaler=False)
+    e.load_state(g["init_params"], np.concatenate([g["init_rm0"], g["init_rv0"], g["init_rm1"], g["init_rv1"]]))
+    x, y = torch.from_numpy(g["x"]).cuda(), torch.from_numpy(g["y"]).cuda()
+    e.reset_counts()
+    got = []
+    for lo in (0, 32, 64):
+        got.append(e.eval_batch(x[lo:lo + 32].contiguous(), y[lo:lo + 32].contiguous()).float().cpu().clone())
+    e.reduce_counts()  # world 1: identity, like dist.reduce on one rank
+    c, s = e.read_counts()
+    logits = torch.cat(got)
+    assert torch.allclose(logits, torch.from_numpy(g["logits"]), rtol=1e-4, atol=1e-5)
+    assert (c, s) == (float(g["correct"]), float(g["size"]))
+    e.close()
+
+
+# ------------------------------------------------------------------ against the CPU oracle
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "fp16", "bf16"])
+@pytest.mark.parametrize("batch", [32, 12])
+def test_step_matches_oracle(dtype, batch):
+    """Same seeds, same synthetic MNIST-shaped inputs; 4 steps.  Scaler decisions bit-exact,
+    loss and gradients within the stated tolerance, every tapped activation compared."""
+    st = _seed_state()
+    amp = dtype != "fp32"
+    e = _engine(dtype=dtype, batch_cap=batch, use_scaler=amp)
+    e.load_state(st.flat_params().numpy(), _bn_of(st))
+    x, y = O.synthetic_mnist(batch * 4)
+    tol = AMP_TOL if amp else FP32_TOL
+    for s in range(4):
+        xs, ys = x[s * batch:(s + 1) * batch], y[s * batch:(s + 1) * batch]
+        before = st.clone()
+        r = O.train_step(st, [xs], [ys], dtype=dtype, use_scaler=amp)
+        e.train_step(xs.cuda().contiguous(), ys.cuda().contiguous())
+        torch.cuda.synchronize()
+        # bit-exact integer / scaler state
+        assert e.found_inf.item() == r.found_inf, f"step {s}"
+        assert e.scale.item() == (st.scale if amp else 1.0)
+        assert e.growth_tracker.item() == (st.growth_tracker if amp else 0)
+        assert e.num_batches_tracked.tolist() == st.num_batches_tracked
+        assert e.loss.item() == pytest.approx(r.losses[0], rel=tol)
+        # forward activations: identical rounding points => (almost) identical values
+        rp = O._RankPass(before, xs, ys, O._DT[dtype])
+        m1 = rp.conv1()
+        m2 = rp.bn1_conv2(m1[0], m1[1])
+        rp.bn2_head(m2[0], m2[1])
+        act = {n: e.read_activation(n, batch) for n in ("y1", "p1", "y2", "p2")}
+        for name, got in act.items():
+            ref = getattr(rp, name)
+            rel = ((got - ref).norm() / ref.norm()).item()
+            assert rel < (2e-3 if amp else 1e-5), f"{name}: rel err {rel}"
+        pr = before.params
+        flips = (count_flips(routing_of(bn_out_from_conv(act["y1"], pr["layer1.1.weight"], pr["layer1.1.bias"], dtype)),
+                             routing_of(rp.a1)) +
+                 count_flips(routing_of(bn_out_from_conv(act["y2"], pr["layer2.1.weight"], pr["layer2.1.bias"], dtype)),
+                             routing_of(rp.a2)))
+        assert flips <= MAX_FLIP_FRACTION * batch * (16 * 196 + 32 * 49)
+        gtol = tol if flips == 0 else (AMP_FLIP_TOL if amp else FP32_FLIP_TOL)
+        if r.found_inf == 0.0:
+            assert_grads_close(e.grads.cpu(), r.grads, gtol, f"{dtype} step {s} ({flips} routing flips)")
+            assert_grads_close(e.grads_scaled.cpu(), r.scaled_grads, gtol, f"{dtype} scaled step {s}")
+        else:
+            assert not torch.isfinite(e.grads_scaled).all()
+    got = e.read_state()
+    assert np.allclose(got["bn_buffers"], _bn_of(st), rtol=1e-3 if amp else 1e-5, atol=1e-6)
+    e.close()
+
+
+# ------------------------------------------------------------------ against the reference's own stack, live
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "fp16", "bf16"])
+def test_step_matches_torch_cuda_reference(dtype):
+    """The real thing: torch's cuDNN/cuBLASLt/ATen kernels + autocast + GradScaler + SGD on
+    this GPU (W=1, so SyncBN == BN, ddp_main.py:120) versus the fused step, 6 steps incl. a
+    ragged tail batch of 12 (60000 % 32 at W=8)."""
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.set_float32_matmul_precision("highest")
+    torch.manual_seed(3407)
+    amp = dtype != "fp32"
+    model = RefConvNet(TDT[dtype], "cuda").cuda()
+    bn_out = {}
+    model.layer1[1].register_forward_hook(lambda m, i, o: bn_out.__setitem__(1, o.detach().float().cpu()))
+    model.layer2[1].register_forward_hook(lambda m, i, o: bn_out.__setitem__(2, o.detach().float().cpu()))
+    tr = RefTrainer(model, amp)
+    e = _engine(dtype=dtype, batch_cap=32, use_scaler=amp)
+    e.load_state(flat_params(model).numpy(), bn_buffers(model).numpy())
+    x, y = O.synthetic_mnist(32 * 5 + 12)
+    x, y = x.cuda(), y.cuda()
+    # fp32: cuDNN's own fp32 convolution algorithms differ from a plain fp32 dot product by
+    # more than 1e-5 on the conv2 weight gradient (K = B*196 reduction), hence 1e-3 here; the
+    # 1e-5 bar is held against the fp64-free CPU reference in test_fp32_golden_origin_main.
+    tol = AMP_TOL if amp else 1e-3
+    bounds = [(i * 32, i * 32 + 32) for i in range(5)] + [(160, 172)]
+    for s, (lo, hi) in enumerate(bounds):
+        xs, ys = x[lo:hi].contiguous(), y[lo:hi].contiguous()
+        sd = {k: v.detach().float().cpu().clone() for k, v in model.state_dict().items()}
+        ref = tr.step(xs, ys)
+        e.train_step(xs, ys)
+        torch.cuda.synchronize()
+        assert e.found_inf.item() == ref["found_inf"], f"step {s}"
+        if amp:
+            assert e.scale.item() == ref["scale"], f"step {s}"
+            assert e.growth_tracker.item() == ref["tracker"], f"step {s}"
+        assert e.loss.item() == pytest.approx(ref["loss"], rel=tol), f"step {s}"
+        n = hi - lo
+        flips = (count_flips(routing_of(bn_out_from_conv(e.read_activation("y1", n), sd["layer1.1.weight"],
+                                                         sd["layer1.1.bias"], dtype)), routing_of(bn_out[1])) +
+                 count_flips(routing_of(bn_out_from_conv(e.read_activation("y2", n), sd["layer2.1.weight"],
+                                                         sd["layer2.1.bias"], dtype)), routing_of(bn_out[2])))
+        assert flips <= MAX_FLIP_FRACTION * n * (16 * 196 + 32 * 49)
+        gtol = tol if flips == 0 else (AMP_FLIP_TOL if amp else FP32_FLIP_TOL)
+        if ref["found_inf"] == 0.0:
+            errs = grad_errors(e.grads.cpu(), ref["grads"])
+            print(f"{dtype} step {s}: {flips} routing flips, max rel-L2 grad err {max(errs.values()):.2e}")
+            assert_grads_close(e.grads.cpu(), ref["grads"], gtol, f"{dtype} step {s} ({flips} routing flips)")
+    got = e.read_state()
+    fp, ini = flat_params(model).numpy(), None
+    assert np.allclose(got["params"], fp, rtol=1e-4 if amp else 1e-5, atol=2e-6 if amp else 1e-7)
+    assert np.allclose(got["bn_buffers"], bn_buffers(model).numpy(), rtol=2e-3 if amp else 1e-5, atol=1e-6)
+    assert list(got["nbt"]) == nbt(model)
+    e.close()
+
+
+def test_fp16_overflow_trajectory_bit_exact():
+    """SURVEY finding 2/7: step 0 always overflows in fp16 (65536 -> inf in the loss dtype);
+    growth to 65536 is followed by exactly one skipped step.  Short growth interval to see it."""
+    st = _seed_state()
+    e = _engine(dtype="fp16", batch_cap=8, growth_interval=3)
+    st.growth_interval = 3
+    e.load_state(st.flat_params().numpy(), _bn_of(st))
+    x, y = O.synthetic_mnist(8 * 10)
+    traj = []
+    for s in range(10):
+        xs, ys = x[s * 8:(s + 1) * 8], y[s * 8:(s + 1) * 8]
+        p0 = e.params.clone()
+        r = O.train_step(st, [xs], [ys], dtype="fp16")
+        e.train_step(xs.cuda().contiguous(), ys.cuda().contiguous())
+        torch.cuda.synchronize()
+        traj.append((e.found_inf.item(), e.scale.item(), e.growth_tracker.item()))
+        assert traj[-1] == (r.found_inf, st.scale, st.growth_tracker)
+        if r.found_inf:
+            assert torch.equal(p0, e.params)  # optimizer.step() skipped
+    assert [t[0] for t in traj] == [1, 0, 0, 0, 1, 0, 0, 0, 1, 0]
+    assert traj[3][1] == 65536.0 and traj[4][1] == 32768.0
+    e.close()
+
+
+@pytest.mark.parametrize("dtype", ["fp16", "bf16"])
+def test_eval_matches_torch_cuda_reference(dtype):
+    """test() (ddp_main.py:96-112) on 1,000 images incl. a ragged last batch; logits against
+    torch's eval forward, counts bit-exact against the reference's counting of OUR logits and
+    equal to its own counts except where the top-2 logits are within a few ulps."""
+    torch.manual_seed(3407)
+    model = RefConvNet(TDT[dtype], "cuda").cuda()
+    x, y = O.synthetic_mnist(1000, seed=5)
+    x, y = x.cuda(), y.cuda()
+    model.train()
+    with torch.no_grad():
+        for i in range(3):
+            model(x[i * 64:(i + 1) * 64])  # move running stats off init
+    e = _engine(dtype=dtype, batch_cap=32)
+    e.load_state(flat_params(model).numpy(), bn_buffers(model).numpy())
+    model.eval()
+    e.reset_counts()
+    size = torch.tensor(0.0).cuda()
+    correct = torch.tensor(0.0).cuda()
+    mine = torch.tensor(0.0).cuda()
+    flips = 0
+    for lo in range(0, 1000, 32):
+        xs, ys = x[lo:lo + 32].contiguous(), y[lo:lo + 32].contiguous()
+        with torch.no_grad():
+            out = model(xs)
+            size += xs.size(0)
+        correct += (out.argmax(1) == ys).type(torch.float).sum()
+        lg = e.eval_batch(xs, ys)
+        mine += (lg.argmax(1) == ys).type(torch.float).sum()
+        assert torch.allclose(lg.float(), out.float(), rtol=AMP_TOL, atol=AMP_TOL * out.float().abs().max().item())
+        top2 = out.float().topk(2, dim=1).values
+        near_tie = (top2[:, 0] - top2[:, 1]).abs() <= 4 * torch.finfo(TDT[dtype]).eps * top2[:, 0].abs().clamp_min(1e-3)
+        flips += int(((lg.argmax(1) != out.argmax(1)) & ~near_tie).sum())
+    c, s = e.read_counts()
+    assert s == size.item() == 1000.0
+    assert c == mine.item()          # in-kernel argmax/count == torch's on the same logits
+    assert flips == 0                # predictions differ from the reference only at near-ties
+    assert abs(c - correct.item()) <= 3
+    e.close()
+
+
+# ------------------------------------------------------------------ execution-mode properties
+
+
+def test_graph_replay_equals_eager_launches_and_is_deterministic():
+    st = _seed_state()
+    x, y = O.synthetic_mnist(32 * 3)
+    outs = []
+    for use_graph in (True, False, True):
+        e = _engine(dtype="fp16", batch_cap=32, use_graph=use_graph)
+        e.load_state(st.flat_params().numpy(), _bn_of(st))
+        for s in range(3):
+            e.train_step(x[s * 32:(s + 1) * 32].cuda().contiguous(), y[s * 32:(s + 1) * 32].cuda().contiguous())
+        torch.cuda.synchronize()
+        outs.append((e.params.cpu().clone(), e.grads.cpu().clone(), e.bn_buffers.cpu().clone(), e.loss.item()))
+        assert e.launch_count() == 13 * 3
+        e.close()
+    for o in outs[1:]:
+        assert torch.equal(o[0], outs[0][0]) and torch.equal(o[1], outs[0][1]) and torch.equal(o[2], outs[0][2])
+        assert o[3] == outs[0][3]
+
+
+def test_host_entry_point_equals_device_entry_point():
+    st = _seed_state()
+    x, y = O.synthetic_mnist(64)
+    a, b = _engine(dtype="fp16", batch_cap=32), _engine(dtype="fp16", batch_cap=32)
+    for e in (a, b):
+        e.load_state(st.flat_params().numpy(), _bn_of(st))
+    xp, yp = x.pin_memory(), y.pin_memory()
+    for s in range(2):
+        a.train_step(x[s * 32:(s + 1) * 32].cuda().contiguous(), y[s * 32:(s + 1) * 32].cuda().contiguous())
+        loss = b.train_step_host(xp[s * 32:(s + 1) * 32], yp[s * 32:(s + 1) * 32])
+        torch.cuda.synchronize()
+        assert loss == a.loss.item()
+    assert torch.equal(a.params, b.params)
+    a.close(); b.close()
+
+
+def test_large_batch_bf16_matches_torch_cuda_reference():
+    """configs[3]: bf16, batch 4096 per GPU."""
+    torch.manual_seed(3407)
+    model = RefConvNet(torch.bfloat16, "cuda").cuda()
+    tr = RefTrainer(model, True)
+    e = _engine(dtype="bf16", batch_cap=4096)
+    e.load_state(flat_params(model).numpy(), bn_buffers(model).numpy())
+    x, y = O.synthetic_mnist(4096 * 2)
+    x, y = x.cuda(), y.cuda()
+    for s in range(2):
+        xs, ys = x[s * 4096:(s + 1) * 4096].contiguous(), y[s * 4096:(s + 1) * 4096].contiguous()
+        ref = tr.step(xs, ys)
+        e.train_step(xs, ys)
+        torch.cuda.synchronize()
+        assert (e.found_inf.item(), e.scale.item(), e.growth_tracker.item()) == (ref["found_inf"], ref["scale"], ref["tracker"])
+        assert e.loss.item() == pytest.approx(ref["loss"], rel=AMP_TOL)
+        assert_grads_close(e.grads.cpu(), ref["grads"], AMP_TOL, f"bf16 B=4096 step {s}")
+    e.close()
+
+
+def test_argument_errors_are_reported():
+    from ddp_practice_b200 import NativeError
+    e = _engine(dtype="fp16", batch_cap=8)
+    x, y = O.synthetic_mnist(16)
+    with pytest.raises(NativeError, match="batch"):
+        e.train_step(x.cuda(), y.cuda())
+    with pytest.raises(NativeError):
+        _engine(world=9)
+    e.close()
