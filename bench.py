@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: one ConvNet training step under DDP + AMP (BASELINE.json).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU path (host cores)
+  torchrun --nproc-per-node N ... bench.py --gpus N ...    # N > 1, one rank per GPU
+
+Workload (config.workload): BASELINE.json configs[1] -- "ddp_main.py ConvNet with AMP autocast
++ GradScaler, batch 32/GPU" (fp16, SyncBN + DDP all-reduce when N > 1).  A step is one pass of
+ddp_main.py:86-93 over one batch of synthetic MNIST-shaped input.  Prints ONE JSON line."""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "ConvNet train imgs/sec (max over ranks)"
+UNIT = "img/s"
+N_TRAIN = 60000  # MNIST-sized resident dataset: 188 MB fp32 > the 126 MB L2
+
+# algorithmic work per image of each kernel: (flops, activation ELEMENTS moved, fp32-input bytes)
+# (DESIGN.md "Kernels" states the same table)
+KERNEL_WORK = {
+    "conv1_fwd": (627200, 12544, 784 * 4), "bn1_relu_pool": (0, 12544 + 3136, 0),
+    "conv2_fwd": (5017600, 3136 + 6272, 0), "bn2_relu_pool": (0, 6272 + 1568, 0),
+    "fc_ce": (62720, 1568 + 1568, 0), "fc_wgrad": (31360, 1568, 0),
+    "bn2_bwd_reduce": (0, 6272 + 1568, 0), "bn2_bwd_apply": (0, 6272 * 2 + 1568, 0),
+    "conv2_wgrad": (5017600, 3136 + 6272, 0), "conv2_dgrad": (5017600, 6272 + 3136, 0),
+    "bn1_bwd_reduce": (0, 12544 + 3136, 0), "conv1_wgrad": (627200, 12544 + 3136, 784 * 4),
+    "step": (0, 0, 0),
+}
+STEP_PARAM_BYTES = 4 * 116136  # params read+write, grads write x2, per step (not per image)
+STEP_BYTES_PER_IMG_AMP = 247744  # SURVEY.md 8(d), materialise-once model
+STEP_FLOPS_PER_IMG = 16401280
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], d["bf16_tflops"], "measured (MEASURED_PEAKS.json, burst)"
+    return 6650.0, 1590.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_reference_run(batch, steps, warmup, budget_s):
+    """Times oracle/reference_step.py (the reference's CPU path) on this host's cores."""
+    import torch
+    from oracle.convnet_oracle import synthetic_mnist
+    from oracle.reference_step import CpuReference
+    ref = CpuReference()
+    x, y = synthetic_mnist(batch * 64)
+    times, loss = ref.timed(x, y, batch, steps, warmup, budget_s)
+    sec = sum(times) / len(times)
+    return {"value": batch / sec, "unit": UNIT, "cores": ref.threads, "kind": "port",
+            "sample": f"{len(times)} steps of origin_main.py's fp32 step, batch {batch}, after {warmup} warm-up; "
+                      f"torch {torch.__version__} CPU kernels, {ref.threads} threads of {os.cpu_count()} host cpus",
+            "ms_per_step": sec * 1e3, "p50_ms": statistics.median(times) * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    b = cpu_reference_run(args.batch, args.steps, args.warmup, budget_s=240.0)
+    line = {"impl": "reference", "metric": METRIC, "value": b["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": b["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, cpu=True),
+            "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": b["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, cpu=False):
+    return {"workload": f"BASELINE.json configs[1]: ddp_main.py ConvNet step, AMP {args.dtype} autocast + GradScaler, "
+                        f"batch {args.batch}/GPU, SyncBN + one-bucket DDP all-reduce when n_gpus > 1"
+                        + (" -- reference arm: the reference's CPU-runnable form of the same step "
+                           "(configs[0], origin_main.py fp32 SGD on the host cores)" if cpu else ""),
+            "batch_per_gpu": args.batch, "global_batch": args.batch * args.gpus,
+            "l2": f"inputs larger than L2: {N_TRAIN} resident images ({N_TRAIN * 784 * 4 / 1e6:.0f} MB fp32), "
+                  "each batch read once per pass; the 2 MB of step activations are L2-resident by construction",
+            "parallelism": f"dp{args.gpus}"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=200)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from ddp_practice_b200 import Engine  # fails loudly without the CUDA library / a GPU
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B, K, W = args.batch, args.steps, args.warmup
+
+    # ---- synthetic dataset, resident in HBM, sharded like DistributedSampler (rank::world)
+    g = torch.Generator().manual_seed(3407)
+    n_local = (N_TRAIN // world // B) * B
+    x_all = (torch.randint(0, 256, (n_local, 1, 28, 28), dtype=torch.uint8, generator=g).float() / 255)
+    y_all = torch.randint(0, 10, (n_local,), generator=g)
+    if world > 1:  # different data per rank
+        x_all = x_all.roll(rank * 997, 0)
+        y_all = y_all.roll(rank * 997, 0)
+    xd, yd = x_all.cuda(), y_all.cuda()
+    nb = n_local // B
+
+    from oracle.reference_step import build_model  # random-init weights of the reference architecture
+    from oracle.convnet_oracle import OracleState
+    st = OracleState.from_state_dict(build_model().state_dict())
+    eng = Engine(dtype=args.dtype, batch_cap=B, rank=rank, world=world, device=local, use_graph=not args.no_graph,
+                 use_scaler=args.dtype != "fp32")
+    eng.connect()
+    bn = torch.cat([st.running_mean[0], st.running_var[0], st.running_mean[1], st.running_var[1]])
+    eng.load_state(st.flat_params().numpy(), bn.numpy())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    def batch(i):
+        j = i % nb
+        return xd[j * B:(j + 1) * B], yd[j * B:(j + 1) * B]
+
+    # ---- device-resident timing: W warm-up, then exactly K steps between two events
+    for i in range(W):
+        eng.train_step(*batch(i))
+    barrier()
+    launches0 = eng.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        ev0.record()
+        for i in range(K):
+            eng.train_step(*batch(W + i))
+        ev1.record()
+        barrier()
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    gpu_launches = eng.launch_count() - launches0
+    eng.check_device()
+
+    # ---- p50 step latency: same loop with an event per step
+    n_lat = min(K, 1000)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_lat + 1)]
+    evs[0].record()
+    for i in range(n_lat):
+        eng.train_step(*batch(i))
+        evs[i + 1].record()
+    barrier()
+    p50_us = max_over_ranks(statistics.median(evs[i].elapsed_time(evs[i + 1]) for i in range(n_lat)) * 1e3)
+
+    # ---- end to end through the public host API: pinned host batch in, loss out, every step
+    xh, yh = x_all[: B * 64].pin_memory(), y_all[: B * 64].pin_memory()
+    k_e2e = min(K, 1000)
+    for i in range(10):
+        eng.train_step_host(xh[(i % 64) * B:(i % 64 + 1) * B], yh[(i % 64) * B:(i % 64 + 1) * B])
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(k_e2e):
+        j = i % 64
+        eng.train_step_host(xh[j * B:(j + 1) * B], yh[j * B:(j + 1) * B], want_loss=True)
+    e1.record()
+    barrier()
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+
+    # ---- per-kernel device times (graph with event nodes), for the roofline of the dominant kernel
+    prof = {}
+    n_prof = 20
+    for i in range(n_prof):
+        for k, v in eng.profile_step(*batch(i), in_graph=True).items():
+            prof[k] = prof.get(k, 0.0) + v / n_prof
+    barrier()
+    hbm_peak, tf_peak, peak_src = peaks()
+    es = 4 if args.dtype == "fp32" else 2
+    dom = max((k for k in prof if k != "step"), key=lambda k: prof[k])
+    fl, ab, xb = KERNEL_WORK[dom]
+    sec = prof[dom] * 1e-3
+    if fl >= 627200 and dom.startswith("conv2"):
+        ach = fl * B / sec / 1e12
+        roof = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak}
+    else:
+        ach = (ab * es + xb) * B / sec / 1e9
+        roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
+    roof.update({"traffic": None, "peak_source": peak_src, "avg_kernel_us": prof[dom] * 1e3,
+                 "how": f"CUDA events between the kernel nodes of the step graph, mean of {n_prof} steps",
+                 "kernel_us": {k: round(v * 1e3, 2) for k, v in prof.items()},
+                 "step_hbm_frac": (STEP_BYTES_PER_IMG_AMP * (es / 2) * B + STEP_PARAM_BYTES) / (ms_total / K * 1e-3) / 1e9 / hbm_peak,
+                 "note": "batch 32 is latency-bound (SURVEY.md 8d): 7.9 MB and 0.52 GFLOP per step"})
+
+    line = {"metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp16": "f16", "bf16": "bf16", "fp32": "f32"}[args.dtype] + " storage, f32 accumulate",
+            "data": "synthetic", "config": workload_config(args), "p50_step_us": p50_us,
+            "clocks": clk.summary(),
+            "e2e": {"value": world * B * k_e2e / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * 784 * 4 + B * 8,
+                    "d2h_bytes_per_step": 4, "steps": k_e2e, "ms_per_step": e2e_ms / k_e2e,
+                    "api": "ddpstep_train_step_host (pinned host batch in, loss out, stream sync every step)"},
+            "gpu_launches": gpu_launches, "roofline": roof}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        b = cpu_reference_run(B, steps=3000, warmup=30, budget_s=12.0)
+        line["cpu_baseline"] = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -267,6 +267,9 @@ static inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ?
 
 struct Recorder {  // keeps the argument structs that hold x / y so graph replays can be re-pointed
   int n = 0;
+  std::vector<cudaEvent_t>* events = nullptr;  // profiling: one event after every kernel
+  cudaStream_t ev_stream = nullptr;
+  bool ev_external = false;
   Conv1Args a_c1;
   FcArgs a_fc;
   Conv1WgradArgs a_c1w;
@@ -279,7 +282,16 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   BnStat* st1 = c->st;
   BnStat* st2 = c->st + 1;
   auto mark = [&]() {
-    if (rec) rec->n++;
+    if (rec) {
+      rec->n++;
+      if (rec->events) {
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        if (rec->ev_external) cudaEventRecordWithFlags(ev, rec->ev_stream, cudaEventRecordExternal);
+        else cudaEventRecord(ev, rec->ev_stream);
+        rec->events->push_back(ev);
+      }
+    }
     c->launches++;
   };
   // 1. conv1 + local BN1 statistics
@@ -337,7 +349,16 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
   const ddpstep_config& cfg = c->cfg;
   const int dbl = cfg.conv_bias_double_round;
   auto mark = [&]() {
-    if (rec) rec->n++;
+    if (rec) {
+      rec->n++;
+      if (rec->events) {
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        if (rec->ev_external) cudaEventRecordWithFlags(ev, rec->ev_stream, cudaEventRecordExternal);
+        else cudaEventRecord(ev, rec->ev_stream);
+        rec->events->push_back(ev);
+      }
+    }
     c->launches++;
   };
   Conv1Args a1{x, c->params, c->y1, nullptr, c->st, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
@@ -534,6 +555,61 @@ extern "C" int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* ho
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpy(host, src[which], std::min((size_t)bytes, sz[which]), cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+static const char* const kTrainKernelNames[13] = {
+    "conv1_fwd", "bn1_relu_pool", "conv2_fwd", "bn2_relu_pool", "fc_ce", "fc_wgrad", "bn2_bwd_reduce",
+    "bn2_bwd_apply", "conv2_wgrad", "conv2_dgrad", "bn1_bwd_reduce", "conv1_wgrad", "step"};
+
+extern "C" const char* ddpstep_kernel_name(int32_t i) { return (i >= 0 && i < 13) ? kTrainKernelNames[i] : ""; }
+
+extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int64_t* y, int32_t batch, int32_t in_graph,
+                                    float* ms_out, int32_t n_out, void* stream) {
+  int rc = check_step_args(ctx, x, batch);
+  if (rc) return rc;
+  if (!y || !ms_out || n_out < 13) return fail(ctx, DDPSTEP_E_ARG, "need labels and room for 13 durations");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  std::vector<cudaEvent_t> evs;
+  cudaEvent_t ev0;
+  CK(cudaEventCreate(&ev0));
+  Recorder rec;
+  rec.events = &evs;
+  cudaError_t e;
+  if (in_graph) {
+    cudaGraph_t graph;
+    cudaGraphExec_t exec;
+    rec.ev_stream = ctx->cap_stream;
+    rec.ev_external = true;
+    const int64_t before = ctx->launches;
+    CK(cudaStreamBeginCapture(ctx->cap_stream, cudaStreamCaptureModeThreadLocal));
+    cudaEventRecordWithFlags(ev0, ctx->cap_stream, cudaEventRecordExternal);
+    e = enqueue<true>(ctx, x, y, batch, ctx->cap_stream, &rec);
+    cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &graph);
+    ctx->launches = before;
+    if (e != cudaSuccess || e2 != cudaSuccess)
+      return fail(ctx, DDPSTEP_E_CUDA, "profile capture failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+    CK(cudaGraphInstantiate(&exec, graph, 0));
+    CK(cudaGraphLaunch(exec, s));
+    ctx->launches += rec.n;
+    CK(cudaStreamSynchronize(s));
+    cudaGraphExecDestroy(exec);
+    cudaGraphDestroy(graph);
+  } else {
+    rec.ev_stream = s;
+    CK(cudaEventRecord(ev0, s));
+    e = enqueue<true>(ctx, x, y, batch, s, &rec);
+    if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "profile launch failed: %s", cudaGetErrorString(e));
+    CK(cudaStreamSynchronize(s));
+  }
+  cudaEvent_t prev = ev0;
+  for (size_t i = 0; i < evs.size() && i < 13; ++i) {
+    CK(cudaEventElapsedTime(&ms_out[i], prev, evs[i]));
+    prev = evs[i];
+  }
+  cudaEventDestroy(ev0);
+  for (cudaEvent_t ev : evs) cudaEventDestroy(ev);
   return 0;
 }
 
