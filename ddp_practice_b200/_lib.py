@@ -50,6 +50,7 @@ SYMBOLS = [
     ("ddpstep_read_activation", C.c_int, [_P, C.c_int32, _P, C.c_int64]),
     ("ddpstep_profile_step", C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, _P, C.c_int32, _P]),
     ("ddpstep_kernel_name", C.c_char_p, [C.c_int32]),
+    ("ddpstep_conv1_bnstats_noalloc", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P, _P, _P]),
     ("ddpstep_launch_count", C.c_int64, [_P]),
     ("ddpstep_device_status", C.c_int, [_P]),
 ]

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -622,5 +623,79 @@ extern "C" int ddpstep_device_status(ddpstep_ctx* ctx) {
   DevState h;
   CK(cudaMemcpy(&h, ctx->ds, sizeof h, cudaMemcpyDeviceToHost));
   if (h.error) return fail(ctx, DDPSTEP_E_PEER, "a peer did not raise its flag within the spin timeout");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------ no-allocation entry point
+// Some hosts of this library are not allowed to allocate device memory at the moment they
+// need a result: a process that has handed its whole memory budget to another allocator (a
+// framework caching pool, a server with a fixed arena carved out at start-up) and treats any
+// later cudaMalloc as a bug or simply has no memory left for one, or a latency-critical loop
+// where cudaMalloc's implicit device-wide synchronisation is the very thing to avoid.
+// ddpstep_create() is useless to them -- it allocates a context.  For those
+// callers the conv1 + BatchNorm-statistics kernel is offered on its own, with the scratch it
+// needs (one row of per-channel partial sums per image, the "last CTA" ticket and the
+// statistics block) living in the library image instead of in cudaMalloc'ed memory.
+namespace {
+
+constexpr int NOALLOC_MAX_BATCH = 1024;  // rows of partial sums held in the static scratch
+
+struct NoAllocScratch {
+  float part[NOALLOC_MAX_BATCH * 16 * 2];  // (sum, sum of squares) per image and channel
+  BnStat st;                               // the kernel's last CTA leaves mean / invstd here
+  DevState ds;                             // only ticket[0] is used; must be 0 at launch
+};
+
+// About 130 KB of global memory on every GPU that loads libddpstep.so, until the process
+// exits.  In host code this name is only a stand-in: its device address comes from
+// cudaGetSymbolAddress below, per device.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_addr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+}  // namespace
+
+extern "C" int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const float* x_dev, int32_t batch, int32_t dtype,
+                                             int32_t conv_bias_double_round, float bn_eps, void* y1_dev,
+                                             float* stats_dev, void* stream) {
+  ddpstep_ctx* ctx = nullptr;  // errors are reported through ddpstep_last_error(NULL)
+  if (!params_dev || !x_dev || !y1_dev || !stats_dev) return fail(nullptr, DDPSTEP_E_ARG, "null device pointer");
+  if (dtype < 0 || dtype > 2) return fail(nullptr, DDPSTEP_E_ARG, "bad dtype %d", dtype);
+  if (batch < 1 || batch > NOALLOC_MAX_BATCH)
+    return fail(nullptr, DDPSTEP_E_ARG,
+                "batch %d is outside [1, %d]: the allocation-free entry point keeps one row of partial sums per "
+                "image in a fixed %zu-byte scratch array; split the batch or use a context (ddpstep_create)",
+                batch, NOALLOC_MAX_BATCH, sizeof(NoAllocScratch));
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(nullptr, DDPSTEP_E_ARG, "device ordinal %d not supported", dev);
+  void* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_addr[dev]) {  // first call on this device: resolve the symbol with this device current
+      void* p = nullptr;
+      CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+      g_noalloc_addr[dev] = p;
+    }
+    base = g_noalloc_addr[dev];
+  }
+  NoAllocScratch* sc = static_cast<NoAllocScratch*>(base);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the array keeps whatever the previous call left: the ticket has to start at zero
+  CK(cudaMemsetAsync(&sc->ds, 0, sizeof(DevState), s));
+  CommDev comm;
+  memset(&comm, 0, sizeof comm);
+  comm.world = 1;
+  Conv1Args a{x_dev, params_dev, y1_dev, sc->part, &sc->st, &sc->ds, comm, batch, conv_bias_double_round, 0, bn_eps};
+  switch (dtype) {
+    case DDPSTEP_FP32: k_conv1_fwd<float><<<batch, 256, 0, s>>>(a); break;
+    case DDPSTEP_FP16: k_conv1_fwd<__half><<<batch, 256, 0, s>>>(a); break;
+    default: k_conv1_fwd<__nv_bfloat16><<<batch, 256, 0, s>>>(a); break;
+  }
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(stats_dev, sc->st.lmean, 16 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  CK(cudaMemcpyAsync(stats_dev + 16, sc->st.linvstd, 16 * sizeof(float), cudaMemcpyDeviceToDevice, s));
   return 0;
 }

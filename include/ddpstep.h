@@ -139,6 +139,26 @@ int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* host, int64_t
 int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
                          int32_t in_graph, float* ms_out, int32_t n_out, void* stream);
 const char* ddpstep_kernel_name(int32_t i);   /* names of those 13 kernels, "" past the end */
+/* conv1 (5x5, pad 2, 1->16 channels) plus the per-channel BatchNorm batch statistics of its
+ * output, WITHOUT a context and without allocating anything.  No counterpart in the
+ * reference: it exists for hosts that cannot call cudaMalloc when they need the result -- a
+ * process whose device memory all belongs to another allocator (a caching pool, a fixed arena
+ * taken at start-up), or a loop that must not hit cudaMalloc's device-wide synchronisation;
+ * such a caller cannot use ddpstep_create, which allocates a context.  Everything
+ * is caller-owned device memory: params_dev = the first 416 floats of the flat parameter
+ * vector (conv1 weight[400], bias[16]); x_dev = [batch,1,28,28] fp32; y1_dev = [batch,16,28,28]
+ * in `dtype`; stats_dev = 32 floats, mean[16] then 1/sqrt(biased var + bn_eps)[16].
+ * Limit: batch <= 1024 (DDPSTEP_E_ARG beyond it, text via ddpstep_last_error(NULL)): the
+ * kernel's scratch -- a row of partial sums per image -- is a fixed array of about 130 KB
+ * inside the library, resident on every GPU that loads it until the process exits.
+ * The target device must be current.  The first call on each device looks that array's
+ * address up; make that first call before starting any stream capture.  All calls share the
+ * one array per device and it keeps the previous call's contents (the call re-zeroes the part
+ * that must start at zero), so two calls whose work overlaps on the GPU -- different streams,
+ * or different threads -- race; order them on one stream or with events.  Asynchronous. */
+int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const float* x_dev, int32_t batch, int32_t dtype,
+                                  int32_t conv_bias_double_round, float bn_eps, void* y1_dev, float* stats_dev,
+                                  void* stream);
 /* Number of kernel launches (graph kernel nodes count one each) issued so far.             */
 int64_t ddpstep_launch_count(const ddpstep_ctx* ctx);
 /* Device-side error word (peer timeout etc.), 0 = healthy.  Synchronises the device.       */
