@@ -49,18 +49,18 @@ template <typename T> __device__ __forceinline__ float conv_out(float acc, float
 // Exchanges are PUSH: the producer stores into every consumer's region and then raises a
 // flag there; consumers spin on their own memory only.  Flags carry a monotonically
 // increasing epoch (never reset), so a stale flag can never satisfy a later wait.
-struct SymRegion {
+struct alignas(128) SymRegion {
   // flags[x][r]: rank r finished pushing exchange x for epoch == value
   unsigned long long flag_bn[4][MAX_WORLD];                // 0 bn1 fwd, 1 bn2 fwd, 2 bn2 bwd, 3 bn1 bwd
   unsigned long long flag_grad[MAX_WORLD][STEP_CTAS];      // per sender rank, per chunk (CTA)
   unsigned long long flag_counts[MAX_WORLD];
   unsigned long long flag_counts_ack;                      // rank 0 consumed this rank's counters
-  float slot_bn_fwd[2][MAX_WORLD][68];                     // mean[C] invstd[C] count   (C <= 32)
-  float slot_bn_bwd[2][MAX_WORLD][64];                     // sum_dy[C] sum_dy_xmu[C]
-  float slot_counts[MAX_WORLD][2];
-  float slot_bnbuf[N_BNBUF];                               // rank 0's running buffers (plain-BN DDP)
-  long long slot_nbt[2];
-  float inbox[2][MAX_WORLD][N_PAD];                        // [step parity][sender rank][bucket]
+  alignas(128) float slot_bn_fwd[2][MAX_WORLD][68];                     // mean[C] invstd[C] count   (C <= 32)
+  alignas(128) float slot_bn_bwd[2][MAX_WORLD][64];                     // sum_dy[C] sum_dy_xmu[C]
+  alignas(128) float slot_counts[MAX_WORLD][2];
+  alignas(128) float slot_bnbuf[N_BNBUF];                               // rank 0's running buffers (plain-BN DDP)
+  alignas(16) long long slot_nbt[2];
+  alignas(128) float inbox[2][MAX_WORLD][N_PAD];                        // [step parity][sender rank][bucket]
 };
 
 struct CommDev {
