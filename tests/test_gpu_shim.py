@@ -1,0 +1,96 @@
+"""The drop-in shim on a GPU: the reference's loop written verbatim against shim objects."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import convnet_oracle as O
+from tests.helpers import assert_grads_close
+from tests.refmodel import RefConvNet, RefTrainer, bn_buffers, flat_grads, flat_params
+
+pytestmark = pytest.mark.gpu
+
+
+def _reference_style_loop(model, batches, criterion, optimizer, scaler):
+    model.train()
+    for images, labels in batches:  # ddp_main.py:85-93
+        images = images.cuda()
+        labels = labels.cuda()
+        outputs = model(images)
+        loss = criterion(outputs, labels)
+        optimizer.zero_grad()
+        scaler.scale(loss).backward()
+        scaler.step(optimizer)
+        scaler.update()
+    return loss
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_shim_runs_the_reference_loop_and_matches_torch(dtype):
+    from ddp_practice_b200 import Engine
+    from ddp_practice_b200.shim import GradScaler, nn
+    torch.manual_seed(3407)
+    ref_model = RefConvNet(dtype, "cuda").cuda()
+    torch.manual_seed(3407)
+    model = RefConvNet(dtype, "cuda").cuda()
+    init_p, init_bn = flat_params(model).numpy(), bn_buffers(model).numpy()
+    # construction sequence of ddp_main.py:117-126
+    model = nn.SyncBatchNorm.convert_sync_batchnorm(model)
+    model = nn.parallel.DistributedDataParallel(model, device_ids=[0])
+    criterion = nn.CrossEntropyLoss().cuda()
+    optimizer = torch.optim.SGD(model.parameters(), 1e-4)
+    scaler = GradScaler()
+    assert model.amp_dtype == {torch.float16: "fp16", torch.bfloat16: "bf16"}[dtype]
+    x, y = O.synthetic_mnist(32 * 4 + 12)
+    batches = [(x[i * 32:(i + 1) * 32], y[i * 32:(i + 1) * 32]) for i in range(4)] + [(x[128:], y[128:])]
+    loss = _reference_style_loop(model, batches, criterion, optimizer, scaler)
+    torch.cuda.synchronize()
+
+    # (1) identical bits to driving the C ABI directly
+    e = Engine(dtype=model.amp_dtype, batch_cap=32)
+    e.load_state(init_p, init_bn)
+    for xb, yb in batches:
+        e.train_step(xb.cuda().contiguous(), yb.cuda().contiguous())
+    torch.cuda.synchronize()
+    assert torch.equal(flat_params(model), e.params.cpu())
+    assert torch.equal(bn_buffers(model), e.bn_buffers.cpu())
+    assert loss.item() == e.loss.item()
+    assert scaler.get_scale() == e.scale.item()
+
+    # (2) tolerance-level agreement with the reference stack
+    tr = RefTrainer(ref_model, True)
+    for xb, yb in batches:
+        rec = tr.step(xb.cuda(), yb.cuda())
+    assert scaler.state_dict() == {"scale": rec["scale"], "growth_factor": 2.0, "backoff_factor": 0.5,
+                                   "growth_interval": 2000, "_growth_tracker": rec["tracker"]}
+    assert loss.item() == pytest.approx(rec["loss"], rel=2e-2)
+    assert_grads_close(flat_grads(model), rec["grads"], 6e-2, "shim p.grad (tap T-c)")
+    assert np.allclose(flat_params(model).numpy(), flat_params(ref_model).numpy(), rtol=1e-4, atol=2e-6)
+
+    # (3) checkpoint surface, ddp_main.py:165-169
+    sd = model.state_dict()
+    assert list(sd.keys()) == ["module." + k for k in ref_model.state_dict().keys()] and len(sd) == 16
+    assert int(sd["module.layer1.1.num_batches_tracked"]) == 5
+
+    # (4) test(), ddp_main.py:96-107
+    model.eval(); ref_model.eval()
+    size = torch.tensor(0.0).cuda(); correct = torch.tensor(0.0).cuda(); ref_correct = torch.tensor(0.0).cuda()
+    xt, yt = O.synthetic_mnist(200, seed=3)
+    for lo in range(0, 200, 32):
+        images, labels = xt[lo:lo + 32].cuda(), yt[lo:lo + 32].cuda()
+        with torch.no_grad():
+            outputs = model(images)
+            size += images.size(0)
+            ref_correct += (ref_model(images).argmax(1) == labels).type(torch.float).sum()
+        correct += (outputs.argmax(1) == labels).type(torch.float).sum()
+    assert size.item() == 200.0 and abs(correct.item() - ref_correct.item()) <= 2
+    e.close()
+
+
+def test_shim_rejects_misuse():
+    from ddp_practice_b200.shim import GradScaler, nn
+    model = nn.parallel.DistributedDataParallel(RefConvNet(torch.float16, "cuda").cuda(), device_ids=[0])
+    opt = torch.optim.SGD(model.parameters(), 1e-4)
+    with pytest.raises(RuntimeError, match="backward"):
+        GradScaler().step(opt)
+    with pytest.raises(NotImplementedError):
+        GradScaler().step(torch.optim.SGD(model.parameters(), 1e-4, momentum=0.9))
