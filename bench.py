@@ -229,15 +229,16 @@ def main():
     p50_us = max_over_ranks(statistics.median(evs[i].elapsed_time(evs[i + 1]) for i in range(n_lat)) * 1e3)
 
     # ---- end to end through the public host API: pinned host batch in, loss out, every step
-    xh, yh = x_all[: B * 64].pin_memory(), y_all[: B * 64].pin_memory()
+    nh = min(64, nb)
+    xh, yh = x_all[: B * nh].pin_memory(), y_all[: B * nh].pin_memory()
     k_e2e = min(K, 1000)
     for i in range(10):
-        eng.train_step_host(xh[(i % 64) * B:(i % 64 + 1) * B], yh[(i % 64) * B:(i % 64 + 1) * B])
+        eng.train_step_host(xh[(i % nh) * B:(i % nh + 1) * B], yh[(i % nh) * B:(i % nh + 1) * B])
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(k_e2e):
-        j = i % 64
+        j = i % nh
         eng.train_step_host(xh[j * B:(j + 1) * B], yh[j * B:(j + 1) * B], want_loss=True)
     e1.record()
     barrier()

@@ -4,13 +4,16 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
+#include <type_traits>
 #include <mutex>
 #include <string>
 #include <vector>
 
 #include "bwd_kernels.cuh"
+#include "conv2_tc.cuh"
 #include "fwd_kernels.cuh"
 #include "step_kernel.cuh"
 
@@ -45,6 +48,8 @@ struct ddpstep_ctx {
   // activations (sized by batch_cap, element size by dtype)
   void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
+  void *p1h = nullptr, *dy2h = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
+  bool use_tc = false;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   float* x_stage = nullptr;
   int64_t* y_stage = nullptr;
@@ -127,6 +132,11 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   A(part1, 296 * 16 * 2 * 4); A(part2, 148 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
   A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
   A(x_stage, B * 784 * 4); A(y_stage, B * 8);
+  {
+    const char* env = getenv("DDPSTEP_TC");
+    ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
+  }
+  if (ctx->use_tc) { A(p1h, B * 2 * PL_BYTES); A(dy2h, B * 4 * PL_BYTES); }
   A(sym, sizeof(SymRegion));
 #undef A
   if (rc) { g_create_error = ctx->err; ddpstep_destroy(ctx); return rc; }
@@ -145,6 +155,10 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<float, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__half, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__nv_bfloat16, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
@@ -180,7 +194,7 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
   void* bufs[] = {ctx->params, ctx->grads, ctx->grads_scaled, ctx->bnbuf, ctx->nbt, ctx->ds, ctx->st, ctx->counts,
                   ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->logits, ctx->dlogits, ctx->dflat, ctx->dy2, ctx->dp1,
                   ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
-                  ctx->y_stage, ctx->sym};
+                  ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h};
   for (void* p : bufs) if (p) cudaFree(p);
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
   delete ctx;
@@ -301,14 +315,23 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   if (rec) rec->a_c1 = a1;
   k_conv1_fwd<T><<<g1, 256, 0, s>>>(a1); mark();
   // 2. BN1 + ReLU + pool
-  BnPoolArgs b1{c->y1, c->p1, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps};
+  BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps};
   k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
   // 3. conv2 + local BN2 statistics
   const int g2 = std::min(B, 148);
   Conv14Args a2{c->p1, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
-  k_conv14<T, 16, 32, 0><<<dim3(g2, 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2); mark();
+  bool tc = false;
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c->use_tc) {  // tcgen05 implicit GEMM on the padded planes written by kernel 2
+      tc = true;
+      Conv2TcArgs t2{c->p1h, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+      k_conv2_tc<T, 0><<<g2, TC_THREADS, tc_smem_bytes(2), s>>>(t2);
+    }
+  }
+  if (!tc) k_conv14<T, 16, 32, 0><<<dim3(g2, 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2);
+  mark();
   // 4. BN2 + ReLU + pool
-  BnPoolArgs b2{c->y2, c->p2, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps};
+  BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps};
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
   // 5. Linear + CE + dlogits + d(pool2 out)
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, c->dlogits, c->dflat, c->nll, c->counts,
@@ -321,7 +344,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   k_fc_wgrad<T><<<dim3(7, nsf), 224, 0, s>>>(fw); mark();
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);
-  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->dy2, c->gpart};
+  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
   k_bn_bwd_reduce<T, 32, 14><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
   k_bn2_bwd_apply<T><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
   // 9. conv2 weight gradient partials, 10. conv2 data gradient
@@ -329,10 +352,19 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   Conv2WgradArgs w2{c->p1, c->dy2, c->gpart, B};
   k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s>>>(w2); mark();
   Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
-  k_conv14<T, 32, 16, 2><<<dim3(std::min(B, 296), 2), 128, (32 * 18 * C14_RS + 8 * 32 * 25) * 4, s>>>(d2); mark();
+  tc = false;
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c->use_tc) {
+      tc = true;
+      Conv2TcArgs t2{c->dy2h, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
+      k_conv2_tc<T, 2><<<std::min(B, 148), TC_THREADS, tc_smem_bytes(4), s>>>(t2);
+    }
+  }
+  if (!tc) k_conv14<T, 32, 16, 2><<<dim3(std::min(B, 296), 2), 128, (32 * 18 * C14_RS + 8 * 32 * 25) * 4, s>>>(d2);
+  mark();
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
   const int ns1 = clampi(cdiv(B, 2), 1, 32);
-  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, nullptr, c->gpart};
+  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, nullptr, nullptr, c->gpart};
   k_bn_bwd_reduce<T, 16, 28><<<dim3(16, ns1), 256, 0, s>>>(r1); mark();
   const int gc1 = std::min(B, 148);
   Conv1WgradArgs cw{r1, x};
@@ -365,11 +397,20 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
   Conv1Args a1{x, c->params, c->y1, nullptr, c->st, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
   k_conv1_fwd<T><<<std::min(B, 296), 256, 0, s>>>(a1); mark();
-  BnPoolArgs b1{c->y1, c->p1, c->params, c->st, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 1, 0, cfg.bn_momentum, cfg.bn_eps};
+  BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, c->st, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 1, 0, cfg.bn_momentum, cfg.bn_eps};
   k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
   Conv14Args a2{c->p1, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
-  k_conv14<T, 16, 32, 0><<<dim3(std::min(B, 148), 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2); mark();
-  BnPoolArgs b2{c->y2, c->p2, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps};
+  bool tc = false;
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c->use_tc) {
+      tc = true;
+      Conv2TcArgs t2{c->p1h, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
+      k_conv2_tc<T, 0><<<std::min(B, 148), TC_THREADS, tc_smem_bytes(2), s>>>(t2);
+    }
+  }
+  if (!tc) k_conv14<T, 16, 32, 0><<<dim3(std::min(B, 148), 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2);
+  mark();
+  BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps};
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1};
   if (rec) rec->a_fc = f;

@@ -82,6 +82,7 @@ struct BnBwdArgs {
   int B, per_split, layer, sync;
   // pass 2 only
   void* dy;           // [B,C,H,H] gradient at the conv output
+  void* dy_planes;    // optional second copy in the padded-plane layout (conv2_tc.cuh), layer 2 only
   float* gpart;       // conv-bias gradient partial rows
 };
 
@@ -216,6 +217,10 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
     }
     store2<T>(dy + off, o[0], o[1]);
     store2<T>(dy + off + H, o[2], o[3]);
+    if (a.dy_planes != nullptr) {
+      T* pl = reinterpret_cast<T*>(a.dy_planes) + (((size_t)(n * 4 + (c >> 3)) * 320 + (2 * ph + 3) * 16 + 2 * pw) * 8 + (c & 7));
+      stf<T>(pl, o[0]); stf<T>(pl + 8, o[1]); stf<T>(pl + 128, o[2]); stf<T>(pl + 136, o[3]);
+    }
   }
   bsum = warp_sum(bsum);
   if ((tid & 31) == 0) red[tid >> 5] = bsum;

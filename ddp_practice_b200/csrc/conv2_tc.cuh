@@ -1,0 +1,289 @@
+// conv2 (5x5, pad 2, 16<->32 channels on 14x14 planes) as an implicit GEMM on the 5th-gen
+// tensor cores: tcgen05.mma with the accumulator in TMEM, operands in shared memory, the
+// image brought in by one TMA bulk copy, a three-role warp-specialised persistent CTA.
+//
+// No im2col is ever materialised.  Activations live in HBM in a "padded plane" layout
+//     [image][channel/8][20 rows x 16 pixels][8 channels]      (16 B per pixel and plane)
+// with image row h at plane row h+3, columns 14..15 and rows 0..2 / 17..19 zero.  Rows being
+// 16 pixels wide, the two zero columns serve as right halo of one row AND left halo of the
+// next, so for output pixel m = h*16 + w the input pixel of filter tap (kh,kw) is simply
+// plane pixel  m + 16*(kh+1) + kw - 2 : a constant shift.  In the K-major, no-swizzle UMMA
+// shared-memory layout one core matrix is 8 rows x 16 B stored contiguously -- exactly 8
+// consecutive pixels of one plane -- so the A operand of every tap is THE SAME staged image
+// addressed through a descriptor whose start address is moved by shift*16 B.  One 128-row MMA
+// covers 8 image rows; an image is two M-tiles (rows 224..255 and columns 14..15 are discarded
+// in the epilogue).  Per image: 2 tiles x 25 taps x (Cin/16) MMAs of 128 x N x 16.
+//
+//   MODE 0  forward        A = p1 planes (Cin 16, 2 planes)   N = 32   D -> y2  (+ BN statistics)
+//   MODE 2  data gradient  A = dy2 planes (Cin 32, 4 planes)  N = 16   D -> d(pool1 out)
+//
+// ddp_main.py:23 (forward) and its autograd (ddp_main.py:91).
+#pragma once
+#include "fwd_kernels.cuh"
+
+namespace dstep {
+
+constexpr int PL_ROWS = 20, PL_PIX = PL_ROWS * 16;     // 320 pixels per plane
+constexpr int PL_BYTES = PL_PIX * 16;                  // 5120 B per plane
+constexpr int TC_THREADS = 192;                        // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
+constexpr int TC_WBYTES = 25 * 1024;                   // 25 taps x (N x K x 2 B = 1 KB)
+constexpr int TC_SLACK = 512;                          // tile 1 of the last plane reads 18 pixels past the plane
+
+__host__ __device__ constexpr int tc_stage_bytes(int planes) { return planes * PL_BYTES + TC_SLACK; }
+__host__ __device__ constexpr int tc_smem_bytes(int planes) { return TC_WBYTES + 2 * tc_stage_bytes(planes) + 256; }
+
+// element offset of (image n, channel c, row h, col w) in a padded-plane tensor with `planes` planes
+__device__ __forceinline__ size_t plane_off(int n, int planes, int c, int h, int w) {
+  return ((size_t)(n * planes + (c >> 3)) * PL_PIX + (h + 3) * 16 + w) * 8 + (c & 7);
+}
+
+// ---- PTX wrappers ---------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc),
+      "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {  // arrives when all MMAs issued so far are done
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// shared-memory matrix descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor):
+// bits [0,14) start>>4, [16,30) leading byte offset>>4 (between the two 8-element K chunks),
+// [32,46) stride byte offset>>4 (between 8-row groups), [46,48) version = 1, [61,64) layout 0
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): D fp32, A/B fp16 or bf16, both K-major, M = 128
+template <typename T> __device__ __forceinline__ uint32_t umma_idesc(int n);
+template <> __device__ __forceinline__ uint32_t umma_idesc<__half>(int n) {
+  return (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
+}
+template <> __device__ __forceinline__ uint32_t umma_idesc<__nv_bfloat16>(int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
+}
+
+template <int N> __device__ __forceinline__ void tmem_ld_row(uint32_t taddr, float* v);
+template <> __device__ __forceinline__ void tmem_ld_row<16>(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+template <> __device__ __forceinline__ void tmem_ld_row<32>(uint32_t taddr, float* v) {
+  tmem_ld_row<16>(taddr, v);
+  tmem_ld_row<16>(taddr + 16, v + 16);
+}
+
+struct Conv2TcArgs {
+  const void* in;      // padded planes: MODE 0 p1h [B][2][320][8], MODE 2 dy2h [B][4][320][8]
+  const float* params;
+  void* out;           // MODE 0 y2 [B,32,14,14], MODE 2 dp1 [B,16,14,14]  (NCHW, T)
+  float* part;         // MODE 0: BN partial sums [gridDim.x][32][2] (nullptr in eval)
+  BnStat* st;
+  DevState* ds;
+  CommDev comm;
+  int B, dbl, sync;
+  float eps;
+};
+
+template <typename T, int MODE>
+__global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
+  constexpr int PLANES = MODE == 0 ? 2 : 4;   // input channel groups of 8
+  constexpr int N = MODE == 0 ? 32 : 16;      // output channels
+  constexpr int KSTEPS = PLANES / 2;          // MMAs (K = 16) per tap
+  constexpr int STAGE = tc_stage_bytes(PLANES);
+  constexpr uint32_t IMG_BYTES = PLANES * PL_BYTES;
+  extern __shared__ __align__(128) unsigned char tc_smem[];
+  unsigned char* w_s = tc_smem;                         // [25][KSTEPS*2 chunks][N rows][8] T
+  unsigned char* in_s = tc_smem + TC_WBYTES;            // [2 stages][PLANES][320][8] T (+ slack)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tc_smem + TC_WBYTES + 2 * STAGE);
+  uint64_t *full = bars, *empty = bars + 2, *tfull = bars + 4, *tempty = bars + 6;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  // ---- one-time setup: filter taps as K-major B tiles, barriers, TMEM
+  T* wt = reinterpret_cast<T*>(w_s);
+  for (int i = tid; i < 25 * N * PLANES * 8; i += TC_THREADS) {
+    const int k8 = i & 7, n = (i >> 3) % N, kc = (i / (8 * N)) % PLANES, tap = i / (8 * N * PLANES);
+    const int k = kc * 8 + k8;
+    float w;
+    if (MODE == 0) w = a.params[OFF_W2 + (n * 16 + k) * 25 + tap];          // B[n=co][k=ci]
+    else           w = a.params[OFF_W2 + (k * 16 + n) * 25 + (24 - tap)];    // B[n=ci][k=co], flipped tap
+    wt[i] = Cvt<T>::from_f(w);
+  }
+  // the slack after each stage is read by discarded rows only, but must not hold NaN patterns that
+  // could trap nothing -- it is plain data; zero it once for reproducible garbage rows
+  for (int i = tid; i < 2 * (TC_SLACK / 4); i += TC_THREADS) {
+    const int s = i / (TC_SLACK / 4), j = i % (TC_SLACK / 4);
+    reinterpret_cast<uint32_t*>(in_s + s * STAGE + IMG_BYTES)[j] = 0u;
+  }
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+      mbar_init(&tfull[s], 1);
+      mbar_init(&tempty[s], 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(128u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes of w_s -> visible to UMMA
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int n_img = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // images of this CTA
+  const unsigned char* gin = reinterpret_cast<const unsigned char*>(a.in);
+
+  if (warp == 0) {
+    // ===== TMA producer: one bulk copy per image =====
+    if (lane == 0) {
+      for (int i = 0; i < n_img; ++i) {
+        const int s = i & 1;
+        mbar_wait(&empty[s], ((i >> 1) & 1) ^ 1);
+        mbar_expect_tx(&full[s], IMG_BYTES);
+        const int n = blockIdx.x + i * gridDim.x;
+        tma_bulk_g2s(in_s + s * STAGE, gin + (size_t)n * IMG_BYTES, IMG_BYTES, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: 2 tiles x 25 taps x KSTEPS instructions per image =====
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc<T>(N);
+      const uint32_t w_addr = smem_u32(w_s);
+      for (int i = 0; i < n_img; ++i) {
+        const int s = i & 1;
+        const uint32_t ph = (i >> 1) & 1;
+        mbar_wait(&tempty[s], ph ^ 1);
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(in_s + s * STAGE);
+#pragma unroll 1
+        for (int tile = 0; tile < 2; ++tile) {
+          const uint32_t d = tmem_base + (uint32_t)((s * 2 + tile) * N);
+#pragma unroll 1
+          for (int tap = 0; tap < 25; ++tap) {
+            const int kh = tap / 5, kw = tap % 5;
+            const uint32_t shift = (uint32_t)(tile * 128 + 16 * (kh + 1) + kw - 2) * 16u;
+#pragma unroll
+            for (int kk = 0; kk < KSTEPS; ++kk) {
+              const uint64_t ad = umma_desc(a_addr + shift + kk * 2 * PL_BYTES, PL_BYTES, 128);
+              const uint64_t bd = umma_desc(w_addr + tap * 1024 + kk * 2 * N * 16, N * 16, 128);
+              umma_f16(d, ad, bd, idesc, (tap | kk) != 0);
+            }
+          }
+        }
+        umma_commit(&empty[s]);   // smem stage may be refilled
+        umma_commit(&tfull[s]);   // accumulators ready
+      }
+    }
+  } else {
+    // ===== epilogue: TMEM -> registers -> bias / rounding / BN statistics -> HBM =====
+    const int q = warp & 3;                      // TMEM lane quarter this warp may touch
+    const int et = q * 32 + lane;                // row within the tile
+    T* __restrict__ out = reinterpret_cast<T*>(a.out);
+    float bias[MODE == 0 ? 32 : 1];
+    float s_sum[MODE == 0 ? 32 : 1], s_sq[MODE == 0 ? 32 : 1];
+    if (MODE == 0) {
+#pragma unroll
+      for (int c = 0; c < 32; ++c) { bias[c] = rnd<T>(a.params[OFF_B2 + c]); s_sum[c] = 0.f; s_sq[c] = 0.f; }
+    }
+    for (int i = 0; i < n_img; ++i) {
+      const int s = i & 1;
+      const int n = blockIdx.x + i * gridDim.x;
+      mbar_wait(&tfull[s], (i >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int tile = 0; tile < 2; ++tile) {
+        float v[N];
+        tmem_ld_row<N>(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((s * 2 + tile) * N), v);
+        const int m = tile * 128 + et, h = m >> 4, w = m & 15;
+        if (h < 14 && w < 14) {
+#pragma unroll
+          for (int c = 0; c < N; ++c) {
+            float o;
+            if (MODE == 0) {
+              o = conv_out<T>(v[c], bias[c], a.dbl);
+              s_sum[c] += o;
+              s_sq[c] = fmaf(o, o, s_sq[c]);
+            } else {
+              o = v[c];
+            }
+            stf<T>(&out[(((size_t)n * N + c) * 14 + h) * 14 + w], o);
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty[s]);
+    }
+    if (MODE == 0 && a.part != nullptr) {
+      // deterministic CTA reduction of the per-thread statistics: butterfly inside the warp, then
+      // the four epilogue warps are summed in a fixed order below
+      float* red = reinterpret_cast<float*>(in_s);  // [4 warps][64]; the image stages are idle by now
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        const float t0 = warp_sum(s_sum[c]), t1 = warp_sum(s_sq[c]);
+        if (lane == 0) { red[q * 64 + c] = t0; red[q * 64 + 32 + c] = t1; }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (MODE == 0 && a.part != nullptr) {
+    const float* red = reinterpret_cast<const float*>(in_s);
+    if (tid < 64) {
+      const float acc = ((red[tid] + red[64 + tid]) + red[128 + tid]) + red[192 + tid];
+      const int c = tid & 31, stat = tid >> 5;
+      a.part[((size_t)blockIdx.x * 32 + c) * 2 + stat] = acc;
+    }
+  }
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+  }
+  if (MODE == 0 && a.part != nullptr) {
+    if (last_cta_done(&a.ds->ticket[1], gridDim.x))
+      finalize_fwd_stats<32>(a.part, gridDim.x, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
+  }
+}
+
+}  // namespace dstep

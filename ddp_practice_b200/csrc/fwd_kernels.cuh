@@ -215,6 +215,7 @@ __global__ void __launch_bounds__(256) k_conv1_fwd(Conv1Args a) {
 struct BnPoolArgs {
   const void* y;
   void* p;
+  void* p_planes;  // optional second copy in the padded-plane layout the tcgen05 conv2 reads (conv2_tc.cuh)
   const float* params;
   BnStat* st;
   float* bnbuf;
@@ -306,6 +307,10 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
     v3 = rnd<T>((v3 - mu) * is * g + b);
     const float m = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
     stf<T>(&p[idx], m);
+    if (C == 16 && a.p_planes != nullptr) {
+      const int n = (int)(plane / C);
+      stf<T>(reinterpret_cast<T*>(a.p_planes) + (((size_t)(n * 2 + (c >> 3)) * 320 + (ph + 3) * 16 + pw) * 8 + (c & 7)), m);
+    }
   }
 }
 
