@@ -48,7 +48,7 @@ struct ddpstep_ctx {
   // activations (sized by batch_cap, element size by dtype)
   void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
-  void *p1h = nullptr, *dy2h = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
+  void *p1h = nullptr, *dy2h = nullptr, *w2_tiles = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
   bool use_tc = false;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   float* x_stage = nullptr;
@@ -60,7 +60,9 @@ struct ddpstep_ctx {
   std::vector<void*> opened;
   // graphs, keyed by batch (train) / -batch (eval with labels) / -batch-100000 (eval, no labels)
   std::map<long, GraphEntry> graphs;
-  cudaStream_t cap_stream = nullptr;
+  cudaStream_t cap_stream = nullptr, side1 = nullptr, side2 = nullptr;
+  cudaEvent_t ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
+  float* gred = nullptr;
   int64_t launches = 0;
   int esize = 2;
 };
@@ -131,12 +133,12 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   A(dp1, B * 16 * 196 * es); A(nll, B * 4);
   A(part1, 296 * 16 * 2 * 4); A(part2, 148 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
   A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
-  A(x_stage, B * 784 * 4); A(y_stage, B * 8);
+  A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4);
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
   }
-  if (ctx->use_tc) { A(p1h, B * 2 * PL_BYTES); A(dy2h, B * 4 * PL_BYTES); }
+  if (ctx->use_tc) { A(p1h, B * 2 * PL_BYTES); A(dy2h, B * 4 * PL_BYTES); A(w2_tiles, 2 * TC_WBYTES); }
   A(sym, sizeof(SymRegion));
 #undef A
   if (rc) { g_create_error = ctx->err; ddpstep_destroy(ctx); return rc; }
@@ -150,8 +152,12 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   cudaError_t e = cudaMemcpy(ctx->bnbuf, bn.data(), N_BNBUF * 4, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(ctx->ds, &h, sizeof h, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side1, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side2, cudaStreamNonBlocking);
+  for (cudaEvent_t* ev : {&ctx->ev_f1, &ctx->ev_j1, &ctx->ev_f2, &ctx->ev_j2})
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
   // kernels that need more than 48 KB of dynamic shared memory
-  const int smem_dgrad = (32 * 18 * C14_RS + 8 * 32 * 25) * 4, smem_c1w = (16 * 784 + 32 * C1_XS) * 4;
+  const int smem_dgrad = (32 * 18 * C14_RS + 8 * 32 * 25) * 4;
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<float, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__half, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__nv_bfloat16, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
@@ -159,9 +165,6 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_c1w);
   if (e != cudaSuccess) {
     fail(nullptr, DDPSTEP_E_CUDA, "context setup failed: %s", cudaGetErrorString(e));
     ddpstep_destroy(ctx);
@@ -194,9 +197,12 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
   void* bufs[] = {ctx->params, ctx->grads, ctx->grads_scaled, ctx->bnbuf, ctx->nbt, ctx->ds, ctx->st, ctx->counts,
                   ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->logits, ctx->dlogits, ctx->dflat, ctx->dy2, ctx->dp1,
                   ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
-                  ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h};
+                  ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h, ctx->w2_tiles, ctx->gred};
   for (void* p : bufs) if (p) cudaFree(p);
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
+  if (ctx->side1) cudaStreamDestroy(ctx->side1);
+  if (ctx->side2) cudaStreamDestroy(ctx->side2);
+  for (cudaEvent_t ev : {ctx->ev_f1, ctx->ev_j1, ctx->ev_f2, ctx->ev_j2}) if (ev) cudaEventDestroy(ev);
   delete ctx;
   return 0;
 }
@@ -237,6 +243,12 @@ extern "C" int ddpstep_load_state(ddpstep_ctx* ctx, const float* params, const f
   CK(cudaMemcpy(ctx->bnbuf, bn, N_BNBUF * 4, cudaMemcpyHostToDevice));
   int64_t z[2] = {0, 0};
   CK(cudaMemcpy(ctx->nbt, nbt ? nbt : z, 16, cudaMemcpyHostToDevice));
+  if (ctx->use_tc) {
+    if (ctx->cfg.dtype == DDPSTEP_FP16) k_refresh_w2_tiles<__half><<<50, 256>>>(ctx->params, ctx->w2_tiles);
+    else k_refresh_w2_tiles<__nv_bfloat16><<<50, 256>>>(ctx->params, ctx->w2_tiles);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+  }
   return 0;
 }
 
@@ -313,7 +325,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   const int g1 = std::min(B, 296);
   Conv1Args a1{x, c->params, c->y1, c->part1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
-  k_conv1_fwd<T><<<g1, 256, 0, s>>>(a1); mark();
+  k_conv1_fwd<T><<<dim3(g1, C1_GROUPS), C1_THREADS, 0, s>>>(a1); mark();
   // 2. BN1 + ReLU + pool
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps};
   k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
@@ -324,7 +336,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {  // tcgen05 implicit GEMM on the padded planes written by kernel 2
       tc = true;
-      Conv2TcArgs t2{c->p1h, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
       k_conv2_tc<T, 0><<<g2, TC_THREADS, tc_smem_bytes(2), s>>>(t2);
     }
   }
@@ -341,7 +353,13 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 6. fc weight/bias gradient partials
   const int nsf = clampi(cdiv(B, 8), 1, 40);
   FcWgradArgs fw{c->p2, c->dlogits, c->gpart, B, cdiv(B, nsf)};
-  k_fc_wgrad<T><<<dim3(7, nsf), 224, 0, s>>>(fw); mark();
+  // the two weight-gradient branches do not feed the activation-gradient chain: they run on side
+  // streams (parallel branches of the captured graph) and join right before the tail kernel
+  const bool fork = !(rec && rec->events);  // per-kernel profiling keeps everything on one stream
+  cudaStream_t s1 = fork ? c->side1 : s, s2 = fork ? c->side2 : s;
+  if (fork) { cudaEventRecord(c->ev_f1, s); cudaStreamWaitEvent(s1, c->ev_f1, 0); }
+  k_fc_wgrad<T><<<dim3(7, nsf), 224, 0, s1>>>(fw); mark();
+  if (fork) cudaEventRecord(c->ev_j1, s1);
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);
   BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
@@ -350,13 +368,16 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 9. conv2 weight gradient partials, 10. conv2 data gradient
   const int gw = std::min(B, 37);
   Conv2WgradArgs w2{c->p1, c->dy2, c->gpart, B};
-  k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s>>>(w2); mark();
+  if (fork) { cudaEventRecord(c->ev_f2, s); cudaStreamWaitEvent(s2, c->ev_f2, 0); }
+  k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s2>>>(w2); mark();
+  k_reduce_rows<<<25, 128, 0, s2>>>(c->gpart, c->gred, gw); mark();
+  if (fork) cudaEventRecord(c->ev_j2, s2);
   Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
   tc = false;
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {
       tc = true;
-      Conv2TcArgs t2{c->dy2h, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
+      Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
       k_conv2_tc<T, 2><<<std::min(B, 148), TC_THREADS, tc_smem_bytes(4), s>>>(t2);
     }
   }
@@ -369,10 +390,11 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   const int gc1 = std::min(B, 148);
   Conv1WgradArgs cw{r1, x};
   if (rec) rec->a_c1w = cw;
-  k_conv1_wgrad<T><<<gc1, 320, (16 * 784 + 32 * C1_XS) * 4, s>>>(cw); mark();
+  k_conv1_wgrad<T><<<dim3(gc1, 4), C1W_THREADS, 0, s>>>(cw); mark();
   // 13. Reducer all-reduce + GradScaler + SGD
-  StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gdirect, c->nll, c->bnbuf, c->nbt, c->ds, c->comm, B,
+  StepArgs sa{c->params, c->w2_tiles, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->bnbuf, c->nbt, c->ds, c->comm, B,
               gc1, gw, ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
+  if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   k_step<T><<<STEP_CTAS, STEP_THREADS, 0, s>>>(sa); mark();
   return cudaGetLastError();
 }
@@ -396,7 +418,7 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
   };
   Conv1Args a1{x, c->params, c->y1, nullptr, c->st, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
-  k_conv1_fwd<T><<<std::min(B, 296), 256, 0, s>>>(a1); mark();
+  k_conv1_fwd<T><<<dim3(std::min(B, 296), C1_GROUPS), C1_THREADS, 0, s>>>(a1); mark();
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, c->st, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 1, 0, cfg.bn_momentum, cfg.bn_eps};
   k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
   Conv14Args a2{c->p1, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
@@ -404,7 +426,7 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {
       tc = true;
-      Conv2TcArgs t2{c->p1h, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
+      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
       k_conv2_tc<T, 0><<<std::min(B, 148), TC_THREADS, tc_smem_bytes(2), s>>>(t2);
     }
   }
@@ -510,6 +532,7 @@ static int run_graph(ddpstep_ctx* ctx, const float* x, const int64_t* y, int B, 
 static int check_step_args(ddpstep_ctx* ctx, const void* x, int32_t batch) {
   if (!ctx) return DDPSTEP_E_ARG;
   if (!x) return fail(ctx, DDPSTEP_E_ARG, "null input pointer");
+  if (reinterpret_cast<uintptr_t>(x) & 15) return fail(ctx, DDPSTEP_E_ARG, "the image pointer must be 16-byte aligned");
   if (batch < 1 || batch > ctx->cfg.batch_cap)
     return fail(ctx, DDPSTEP_E_ARG, "batch %d outside [1, batch_cap=%d]", batch, ctx->cfg.batch_cap);
   if (!ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "world > 1: call ddpstep_import_peers first");
@@ -600,17 +623,18 @@ extern "C" int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* ho
   return 0;
 }
 
-static const char* const kTrainKernelNames[13] = {
+constexpr int kTrainKernels = 14;
+static const char* const kTrainKernelNames[kTrainKernels] = {
     "conv1_fwd", "bn1_relu_pool", "conv2_fwd", "bn2_relu_pool", "fc_ce", "fc_wgrad", "bn2_bwd_reduce",
-    "bn2_bwd_apply", "conv2_wgrad", "conv2_dgrad", "bn1_bwd_reduce", "conv1_wgrad", "step"};
+    "bn2_bwd_apply", "conv2_wgrad", "conv2_wgrad_reduce", "conv2_dgrad", "bn1_bwd_reduce", "conv1_wgrad", "step"};
 
-extern "C" const char* ddpstep_kernel_name(int32_t i) { return (i >= 0 && i < 13) ? kTrainKernelNames[i] : ""; }
+extern "C" const char* ddpstep_kernel_name(int32_t i) { return (i >= 0 && i < kTrainKernels) ? kTrainKernelNames[i] : ""; }
 
 extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int64_t* y, int32_t batch, int32_t in_graph,
                                     float* ms_out, int32_t n_out, void* stream) {
   int rc = check_step_args(ctx, x, batch);
   if (rc) return rc;
-  if (!y || !ms_out || n_out < 13) return fail(ctx, DDPSTEP_E_ARG, "need labels and room for 13 durations");
+  if (!y || !ms_out || n_out < kTrainKernels) return fail(ctx, DDPSTEP_E_ARG, "need labels and room for 14 durations");
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   std::vector<cudaEvent_t> evs;
@@ -646,7 +670,7 @@ extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int6
     CK(cudaStreamSynchronize(s));
   }
   cudaEvent_t prev = ev0;
-  for (size_t i = 0; i < evs.size() && i < 13; ++i) {
+  for (size_t i = 0; i < evs.size() && i < (size_t)kTrainKernels; ++i) {
     CK(cudaEventElapsedTime(&ms_out[i], prev, evs[i]));
     prev = evs[i];
   }
@@ -731,9 +755,9 @@ extern "C" int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const floa
   comm.world = 1;
   Conv1Args a{x_dev, params_dev, y1_dev, sc->part, &sc->st, &sc->ds, comm, batch, conv_bias_double_round, 0, bn_eps};
   switch (dtype) {
-    case DDPSTEP_FP32: k_conv1_fwd<float><<<batch, 256, 0, s>>>(a); break;
-    case DDPSTEP_FP16: k_conv1_fwd<__half><<<batch, 256, 0, s>>>(a); break;
-    default: k_conv1_fwd<__nv_bfloat16><<<batch, 256, 0, s>>>(a); break;
+    case DDPSTEP_FP32: k_conv1_fwd<float><<<dim3(batch, C1_GROUPS), C1_THREADS, 0, s>>>(a); break;
+    case DDPSTEP_FP16: k_conv1_fwd<__half><<<dim3(batch, C1_GROUPS), C1_THREADS, 0, s>>>(a); break;
+    default: k_conv1_fwd<__nv_bfloat16><<<dim3(batch, C1_GROUPS), C1_THREADS, 0, s>>>(a); break;
   }
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(stats_dev, sc->st.lmean, 16 * sizeof(float), cudaMemcpyDeviceToDevice, s));

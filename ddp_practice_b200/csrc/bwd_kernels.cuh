@@ -125,6 +125,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
     const bool xchg = a.sync && a.comm.world > 1;
     if (tid < C) {
       double s0 = 0.0, s1 = 0.0;
+#pragma unroll 8
       for (int s = 0; s < (int)gridDim.y; ++s) {
         s0 += (double)__ldcg(&a.bpart[((size_t)tid * gridDim.y + s) * 2]);
         s1 += (double)__ldcg(&a.bpart[((size_t)tid * gridDim.y + s) * 2 + 1]);
@@ -299,90 +300,105 @@ __global__ void __launch_bounds__(160) k_conv2_wgrad(Conv2WgradArgs a) {
 // BN1 backward pass 2 fused with the conv1 weight / bias gradient (conv1's input needs no
 // gradient, so d(conv1 out) lives only in shared memory):
 //   dW1[co][kh][kw] = sum_{n,h,w} dy1[n,co,h,w] * x[n,h+kh-2,w+kw-2],  db1[co] = sum dy1
-// 320 threads: phase A one pooling window per thread-iteration, phase B thread = (co, kh,
-// quarter of the rows) with a 5-wide kw register tile.
+// CTA = one image x 4 channels (grid.y = 4), 160 threads.  Phase A: one pooling window per
+// thread-iteration -> dy1 in shared memory.  Phase B: thread = (channel, kh, 4 of the 28 rows)
+// with a 5-wide kw register tile.
 struct Conv1WgradArgs {
   BnBwdArgs bn;    // y = y1, dpool = d(pool1 out), layer = 0
   const float* x;  // [B,784] fp32
 };
 
+constexpr int C1W_THREADS = 160;
+
 template <typename T>
-__global__ void __launch_bounds__(320) k_conv1_wgrad(Conv1WgradArgs a) {
-  extern __shared__ __align__(16) float smem[];
-  float* dy_s = smem;                // [16][28][28]
-  float* xs = smem + 16 * 784;       // [32][C1_XS]
-  __shared__ float s_k1[16], s_k2[16], s_mu[16], s_is[16], s_g[16], s_b[16];
+__global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
+  __shared__ __align__(16) float dy_s[4 * 784];
+  __shared__ __align__(16) float xs[32 * C1_XS];
+  __shared__ float red[140][6];
+  __shared__ float s_k1[16], s_k2[16];
   bn_backward_sums<16>(a.bn, s_k1, s_k2);
-  const int tid = threadIdx.x;
-  if (tid < 16) {
-    s_mu[tid] = a.bn.st->mean[tid];
-    s_is[tid] = a.bn.st->invstd[tid];
-    s_g[tid] = a.bn.params[OFF_G1 + tid];
-    s_b[tid] = a.bn.params[OFF_BE1 + tid];
-  }
-  for (int i = tid; i < 32 * C1_XS; i += 320) xs[i] = 0.f;
+  const int tid = threadIdx.x, cg = blockIdx.y;
+  for (int i = tid; i < 32 * C1_XS; i += C1W_THREADS) xs[i] = 0.f;
   const T* __restrict__ y1 = reinterpret_cast<const T*>(a.bn.y);
   const T* __restrict__ dp1 = reinterpret_cast<const T*>(a.bn.dpool);
-  const int rs = tid & 3, kh = (tid >> 2) % 5, co = tid / 20;
+  const int rs = tid % 7, kh = (tid / 7) % 5, col = tid / 35;  // valid for tid < 140
   float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f}, bsum = 0.f;
 
   for (int n = blockIdx.x; n < a.bn.B; n += gridDim.x) {
     __syncthreads();
-    for (int i = tid; i < 784; i += 320) xs[(i / 28 + 2) * C1_XS + i % 28 + 2] = rnd<T>(a.x[(size_t)n * 784 + i]);
-    for (int e = tid; e < 16 * 196; e += 320) {
-      const int c = e / 196, w = e % 196, ph = w / 14, pw = w % 14;
-      const size_t off = (((size_t)n * 16 + c) * 28 + 2 * ph) * 28 + 2 * pw;
-      float v[4];
-      load2<T>(y1 + off, v[0], v[1]);
-      load2<T>(y1 + off + 28, v[2], v[3]);
-      const float mu = s_mu[c], is = s_is[c], g = s_g[c];
-      bool live;
-      const int arg = pool_winner<T>(v, mu, is, g, s_b[c], live);
-      const float d = live ? ldf<T>(&dp1[((size_t)n * 16 + c) * 196 + w]) : 0.f;
-      const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
-      float o[4];
+    for (int i = tid; i < 196; i += C1W_THREADS) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(a.x + (size_t)n * 784) + i);
+      float* d = &xs[((4 * i) / 28 + 2) * C1_XS + (4 * i) % 28 + 2];
+      d[0] = rnd<T>(v.x); d[1] = rnd<T>(v.y); d[2] = rnd<T>(v.z); d[3] = rnd<T>(v.w);
+    }
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float da = (live && i == arg) ? d : 0.f;
-        o[i] = rnd<T>((da - k1 - (v[i] - mu) * k2) * k3);
+    for (int it = 0; it < 5; ++it) {
+      const int e = tid + it * C1W_THREADS;
+      if (e < 784) {
+        const int cl = e / 196, w = e % 196, ph = w / 14, pw = w % 14, c = cg * 4 + cl;
+        const size_t off = (((size_t)n * 16 + c) * 28 + 2 * ph) * 28 + 2 * pw;
+        float v[4];
+        load2<T>(y1 + off, v[0], v[1]);
+        load2<T>(y1 + off + 28, v[2], v[3]);
+        const float dd = ldf<T>(&dp1[((size_t)n * 16 + c) * 196 + w]);
+        const float mu = a.bn.st->mean[c], is = a.bn.st->invstd[c], g = a.bn.params[OFF_G1 + c];
+        bool live;
+        const int arg = pool_winner<T>(v, mu, is, g, a.bn.params[OFF_BE1 + c], live);
+        const float d = live ? dd : 0.f;
+        const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
+        float* dst = dy_s + (cl * 28 + 2 * ph) * 28 + 2 * pw;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float da = (live && i == arg) ? d : 0.f;
+          dst[(i >> 1) * 28 + (i & 1)] = rnd<T>((da - k1 - (v[i] - mu) * k2) * k3);
+        }
       }
-      float* dst = dy_s + (c * 28 + 2 * ph) * 28 + 2 * pw;
-      dst[0] = o[0]; dst[1] = o[1]; dst[28] = o[2]; dst[29] = o[3];
     }
     __syncthreads();
-    for (int h = rs * 7; h < rs * 7 + 7; ++h) {
-      const float* drow = dy_s + (co * 28 + h) * 28;
-      const float* xrow = xs + (h + kh) * C1_XS;
+    if (tid < 140) {
 #pragma unroll
-      for (int q = 0; q < 7; ++q) {
-        const float4 d = *reinterpret_cast<const float4*>(drow + 4 * q);
-        const float4 u = *reinterpret_cast<const float4*>(xrow + 4 * q);
-        const float4 v = *reinterpret_cast<const float4*>(xrow + 4 * q + 4);
-        const float xv[8] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w};
+      for (int hh = 0; hh < 4; ++hh) {
+        const int h = rs * 4 + hh;
+        const float* drow = dy_s + (col * 28 + h) * 28;
+        const float* xrow = xs + (h + kh) * C1_XS;
 #pragma unroll
-        for (int kw = 0; kw < 5; ++kw) {
-          acc[kw] = fmaf(d.x, xv[kw], acc[kw]);
-          acc[kw] = fmaf(d.y, xv[kw + 1], acc[kw]);
-          acc[kw] = fmaf(d.z, xv[kw + 2], acc[kw]);
-          acc[kw] = fmaf(d.w, xv[kw + 3], acc[kw]);
+        for (int q = 0; q < 7; ++q) {
+          const float4 d = *reinterpret_cast<const float4*>(drow + 4 * q);
+          const float4 u = *reinterpret_cast<const float4*>(xrow + 4 * q);
+          const float4 v = *reinterpret_cast<const float4*>(xrow + 4 * q + 4);
+          const float xv[8] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int kw = 0; kw < 5; ++kw) {
+            acc[kw] = fmaf(d.x, xv[kw], acc[kw]);
+            acc[kw] = fmaf(d.y, xv[kw + 1], acc[kw]);
+            acc[kw] = fmaf(d.z, xv[kw + 2], acc[kw]);
+            acc[kw] = fmaf(d.w, xv[kw + 3], acc[kw]);
+          }
+          if (kh == 0) bsum += (d.x + d.y) + (d.z + d.w);
         }
-        if (kh == 0) bsum += (d.x + d.y) + (d.z + d.w);
       }
     }
   }
-  // reduce over the 4 row-quarters (adjacent lanes)
+  // fixed-order reduction over the 7 row groups
+  if (tid < 140) {
 #pragma unroll
-  for (int kw = 0; kw < 5; ++kw) {
-    acc[kw] += __shfl_xor_sync(0xffffffffu, acc[kw], 1);
-    acc[kw] += __shfl_xor_sync(0xffffffffu, acc[kw], 2);
+    for (int kw = 0; kw < 5; ++kw) red[tid][kw] = acc[kw];
+    red[tid][5] = bsum;
   }
-  bsum += __shfl_xor_sync(0xffffffffu, bsum, 1);
-  bsum += __shfl_xor_sync(0xffffffffu, bsum, 2);
-  if (rs == 0) {
-    float* row = a.bn.gpart + (size_t)blockIdx.x * N_PAD;
+  __syncthreads();
+  float* row = a.bn.gpart + (size_t)blockIdx.x * N_PAD;
+  if (tid < 100) {  // (col, kh, kw)
+    const int cl = tid / 25, k = tid % 25, kh2 = k / 5, kw2 = k % 5;
+    float v = 0.f;
 #pragma unroll
-    for (int kw = 0; kw < 5; ++kw) row[OFF_W1 + co * 25 + kh * 5 + kw] = acc[kw];
-    if (kh == 0) row[OFF_B1 + co] = bsum;
+    for (int r = 0; r < 7; ++r) v += red[(cl * 5 + kh2) * 7 + r][kw2];
+    row[OFF_W1 + (cg * 4 + cl) * 25 + k] = v;
+  } else if (tid < 104) {
+    const int cl = tid - 100;
+    float v = 0.f;
+#pragma unroll
+    for (int r = 0; r < 7; ++r) v += red[(cl * 5 + 0) * 7 + r][5];
+    row[OFF_B1 + cg * 4 + cl] = v;
   }
 }
 

@@ -110,6 +110,7 @@ template <> __device__ __forceinline__ void tmem_ld_row<32>(uint32_t taddr, floa
 }
 
 struct Conv2TcArgs {
+  const void* wtiles;  // [25][1 KB] B operand tiles for this MODE (step_kernel.cuh: w2_tile_store)
   const void* in;      // padded planes: MODE 0 p1h [B][2][320][8], MODE 2 dy2h [B][4][320][8]
   const float* params;
   void* out;           // MODE 0 y2 [B,32,14,14], MODE 2 dp1 [B,16,14,14]  (NCHW, T)
@@ -132,20 +133,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
   unsigned char* w_s = tc_smem;                         // [25][KSTEPS*2 chunks][N rows][8] T
   unsigned char* in_s = tc_smem + TC_WBYTES;            // [2 stages][PLANES][320][8] T (+ slack)
   uint64_t* bars = reinterpret_cast<uint64_t*>(tc_smem + TC_WBYTES + 2 * STAGE);
-  uint64_t *full = bars, *empty = bars + 2, *tfull = bars + 4, *tempty = bars + 6;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t *full = bars, *empty = bars + 2, *tfull = bars + 4, *tempty = bars + 6, *wbar = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  // ---- one-time setup: filter taps as K-major B tiles, barriers, TMEM
-  T* wt = reinterpret_cast<T*>(w_s);
-  for (int i = tid; i < 25 * N * PLANES * 8; i += TC_THREADS) {
-    const int k8 = i & 7, n = (i >> 3) % N, kc = (i / (8 * N)) % PLANES, tap = i / (8 * N * PLANES);
-    const int k = kc * 8 + k8;
-    float w;
-    if (MODE == 0) w = a.params[OFF_W2 + (n * 16 + k) * 25 + tap];          // B[n=co][k=ci]
-    else           w = a.params[OFF_W2 + (k * 16 + n) * 25 + (24 - tap)];    // B[n=ci][k=co], flipped tap
-    wt[i] = Cvt<T>::from_f(w);
-  }
+  // ---- one-time setup: barriers, TMEM, and the 25 filter taps (ready-made K-major B tiles kept
+  // up to date by the SGD kernel) fetched with one TMA copy
   // the slack after each stage is read by discarded rows only, but must not hold NaN patterns that
   // could trap nothing -- it is plain data; zero it once for reproducible garbage rows
   for (int i = tid; i < 2 * (TC_SLACK / 4); i += TC_THREADS) {
@@ -159,7 +152,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       mbar_init(&tfull[s], 1);
       mbar_init(&tempty[s], 128);
     }
+    mbar_init(wbar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(wbar, TC_WBYTES);
+    tma_bulk_g2s(w_s, a.wtiles, TC_WBYTES, wbar);
   }
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(128u)
@@ -190,6 +186,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
     if (lane == 0) {
       const uint32_t idesc = umma_idesc<T>(N);
       const uint32_t w_addr = smem_u32(w_s);
+      mbar_wait(wbar, 0);
       for (int i = 0; i < n_img; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;

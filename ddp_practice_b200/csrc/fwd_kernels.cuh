@@ -58,13 +58,27 @@ template <> __device__ __forceinline__ void store2<__nv_bfloat16>(__nv_bfloat16*
 template <int C>
 __device__ void finalize_fwd_stats(const float* part, int rows, float count, float eps, BnStat* st, int layer,
                                    const CommDev& comm, DevState* ds, int sync) {
-  const int c = threadIdx.x;
+  // all threads of the CTA take part: column = (channel, statistic), several row lanes per column,
+  // so the loads from the partial buffer overlap instead of forming one long dependent chain
+  __shared__ double fin[512];
+  constexpr int COLS = 2 * C;
+  const int t = threadIdx.x;
+  const int lanes = min((int)blockDim.x / COLS, 512 / COLS);
+  const int col = t % COLS, lane = t / COLS;
+  if (lane < lanes) {
+    double acc = 0.0;
+#pragma unroll 4
+    for (int r = lane; r < rows; r += lanes) acc += (double)__ldcg(&part[(size_t)r * COLS + col]);
+    fin[lane * COLS + col] = acc;
+  }
+  __syncthreads();
+  const int c = t;
   const bool xchg = sync && comm.world > 1;
   if (c < C) {
     double s = 0.0, ss = 0.0;
-    for (int r = 0; r < rows; ++r) {
-      s += (double)__ldcg(&part[(r * C + c) * 2]);
-      ss += (double)__ldcg(&part[(r * C + c) * 2 + 1]);
+    for (int l = 0; l < lanes; ++l) {
+      s += fin[l * COLS + 2 * c];
+      ss += fin[l * COLS + 2 * c + 1];
     }
     double mean = s / (double)count;
     double var = ss / (double)count - mean * mean;
@@ -90,10 +104,11 @@ __device__ void finalize_fwd_stats(const float* part, int rows, float count, flo
 }
 
 // ---------------------------------------------------------------------------------------
-// conv1: x fp32 [B,1,28,28] -> y1 T [B,16,28,28].  CTA = 2 channel groups x 98 tiles of
-// 2x4 pixels, one image at a time (grid-stride over images).  K = 25 makes this a
-// bandwidth kernel: the image is staged once in shared memory, every output is written once
-// with 8/16-byte stores, the BN reduction rides in the epilogue.
+// conv1: x fp32 [B,1,28,28] -> y1 T [B,16,28,28].  CTA = one image x 4 output channels
+// (grid.y = 4 channel groups, so a batch of 32 already fills 128 SMs), thread = one 2x4 pixel
+// tile x 4 channels, grid-stride over images.  K = 25 makes this a bandwidth kernel: the image
+// is staged once in shared memory, every output is written once with 8/16-byte stores, the BN
+// reduction rides in the epilogue.
 struct Conv1Args {
   const float* x;
   const float* params;
@@ -106,36 +121,39 @@ struct Conv1Args {
   float eps;
 };
 
-constexpr int C1_XS = 36;  // padded row stride of the staged image
+constexpr int C1_XS = 36;       // padded row stride of the staged image
+constexpr int C1_THREADS = 128; // 98 active tiles
+constexpr int C1_GROUPS = 4;    // gridDim.y
 
 template <typename T>
-__global__ void __launch_bounds__(256) k_conv1_fwd(Conv1Args a) {
+__global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
   __shared__ __align__(16) float xs[32 * C1_XS];
-  __shared__ __align__(16) float ws[25 * 16];
-  __shared__ float bs[16];
-  __shared__ float red[8][16];
-  const int tid = threadIdx.x;
+  __shared__ __align__(16) float ws[25 * 4];
+  __shared__ float bs[4];
+  __shared__ float red[4][8];
+  const int tid = threadIdx.x, cg = blockIdx.y;
   T* __restrict__ y1 = reinterpret_cast<T*>(a.y1);
 
-  for (int i = tid; i < 32 * C1_XS; i += 256) xs[i] = 0.f;
-  for (int i = tid; i < 400; i += 256) {  // ws[k][co] <- rnd(W1[co][k])
-    int co = i / 25, k = i % 25;
-    ws[k * 16 + co] = rnd<T>(a.params[OFF_W1 + i]);
+  for (int i = tid; i < 32 * C1_XS; i += C1_THREADS) xs[i] = 0.f;
+  if (tid < 100) {  // ws[k][j] <- rnd(W1[cg*4+j][k])
+    const int j = tid / 25, k = tid % 25;
+    ws[k * 4 + j] = rnd<T>(a.params[OFF_W1 + (cg * 4 + j) * 25 + k]);
   }
-  if (tid < 16) bs[tid] = rnd<T>(a.params[OFF_B1 + tid]);
+  if (tid < 4) bs[tid] = rnd<T>(a.params[OFF_B1 + cg * 4 + tid]);
 
-  const int cg = tid >> 7, tile = tid & 127;
-  const bool active = tile < 98;
-  const int tr = tile / 7, tc = tile % 7;
-  float s[8], ss[8];
+  const bool active = tid < 98;
+  const int tr = tid / 7, tc = tid % 7;
+  float s[4], ss[4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) s[j] = ss[j] = 0.f;
+  for (int j = 0; j < 4; ++j) s[j] = ss[j] = 0.f;
 
   for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
     __syncthreads();
-    for (int i = tid; i < 784; i += 256) {
-      int r = i / 28, c = i % 28;
-      xs[(r + 2) * C1_XS + c + 2] = rnd<T>(a.x[(size_t)n * 784 + i]);
+    for (int i = tid; i < 196; i += C1_THREADS) {  // 784 floats as 196 float4
+      const float4 v = __ldg(reinterpret_cast<const float4*>(a.x + (size_t)n * 784) + i);
+      const int r = (4 * i) / 28, c = (4 * i) % 28;
+      float* d = &xs[(r + 2) * C1_XS + c + 2];
+      d[0] = rnd<T>(v.x); d[1] = rnd<T>(v.y); d[2] = rnd<T>(v.z); d[3] = rnd<T>(v.w);
     }
     __syncthreads();
     if (!active) continue;
@@ -147,33 +165,32 @@ __global__ void __launch_bounds__(256) k_conv1_fwd(Conv1Args a) {
       in[r][0] = u.x; in[r][1] = u.y; in[r][2] = u.z; in[r][3] = u.w;
       in[r][4] = v.x; in[r][5] = v.y; in[r][6] = v.z; in[r][7] = v.w;
     }
-    float acc[2][4][8];
+    float acc[2][4][4];
 #pragma unroll
     for (int r = 0; r < 2; ++r)
 #pragma unroll
       for (int c = 0; c < 4; ++c)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[r][c][j] = 0.f;
+        for (int j = 0; j < 4; ++j) acc[r][c][j] = 0.f;
 #pragma unroll
     for (int kh = 0; kh < 5; ++kh)
 #pragma unroll
       for (int kw = 0; kw < 5; ++kw) {
-        const float4 w0 = *reinterpret_cast<const float4*>(&ws[(kh * 5 + kw) * 16 + cg * 8]);
-        const float4 w1 = *reinterpret_cast<const float4*>(&ws[(kh * 5 + kw) * 16 + cg * 8 + 4]);
-        const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+        const float4 w0 = *reinterpret_cast<const float4*>(&ws[(kh * 5 + kw) * 4]);
+        const float w[4] = {w0.x, w0.y, w0.z, w0.w};
 #pragma unroll
         for (int r = 0; r < 2; ++r)
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
             const float v = in[r + kh][c + kw];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[r][c][j] = fmaf(v, w[j], acc[r][c][j]);
+            for (int j = 0; j < 4; ++j) acc[r][c][j] = fmaf(v, w[j], acc[r][c][j]);
           }
       }
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int ch = cg * 8 + j;
-      const float b = bs[ch];
+    for (int j = 0; j < 4; ++j) {
+      const int ch = cg * 4 + j;
+      const float b = bs[j];
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
         float v[4];
@@ -188,22 +205,20 @@ __global__ void __launch_bounds__(256) k_conv1_fwd(Conv1Args a) {
     }
   }
   if (a.part == nullptr) return;  // eval: running statistics are used, none are gathered
-  // CTA reduction of the statistics: warps are channel-group pure (4 warps per group)
   __syncthreads();
   const int warp = tid >> 5, lane = tid & 31;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
+  for (int j = 0; j < 4; ++j) {
     float v = warp_sum(s[j]), q = warp_sum(ss[j]);
-    if (lane == 0) { red[warp][j] = v; red[warp][8 + j] = q; }
+    if (lane == 0) { red[warp][j] = v; red[warp][4 + j] = q; }
   }
   __syncthreads();
-  if (tid < 32) {  // tid = stat*16 + ch
-    const int stat = tid >> 4, ch = tid & 15, g = ch >> 3, j = ch & 7;
-    float v = 0.f;
-    for (int w = 0; w < 4; ++w) v += red[g * 4 + w][stat * 8 + j];
-    a.part[((size_t)blockIdx.x * 16 + ch) * 2 + stat] = v;
+  if (tid < 8) {  // tid = stat*4 + j
+    const int stat = tid >> 2, j = tid & 3;
+    const float v = ((red[0][tid] + red[1][tid]) + red[2][tid]) + red[3][tid];
+    a.part[((size_t)blockIdx.x * 16 + cg * 4 + j) * 2 + stat] = v;
   }
-  if (last_cta_done(&a.ds->ticket[0], gridDim.x))
+  if (last_cta_done(&a.ds->ticket[0], gridDim.x * gridDim.y))
     finalize_fwd_stats<16>(a.part, gridDim.x, (float)a.B * 784.f, a.eps, a.st, 0, a.comm, a.ds, a.sync);
 }
 

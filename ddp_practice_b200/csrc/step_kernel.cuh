@@ -22,9 +22,11 @@ namespace cg = cooperative_groups;
 
 struct StepArgs {
   float* params;
+  void* w2_tiles;       // [2][25][1 KB] conv2 filter as UMMA B tiles (fwd, dgrad) in the autocast dtype; may be null
   float* grads;         // tap T-c
   float* grads_scaled;  // tap T-b
   const float* gpart;   // [rows][N_PAD]
+  const float* gred;    // [N_PAD] conv2-weight partial rows already summed (k_reduce_rows), or null
   const float* gdirect; // [N_PAD]
   const float* nll;     // [B]
   float* bnbuf;
@@ -37,6 +39,42 @@ struct StepArgs {
   float lr, growth_factor, backoff_factor;
   int growth_interval;
 };
+
+// conv2's filter is kept, besides its fp32 master copy, as ready-made tcgen05 B operands
+// (conv2_tc.cuh): 25 taps x [K chunk][N row][8] in the autocast dtype, once for the forward
+// (N = co, K = ci) and once for the data gradient (N = ci, K = co, taps flipped).  The SGD
+// kernel refreshes them as it writes the updated weights, so the conv kernels fetch 25 KB
+// with a single TMA copy instead of converting weights on every launch (the reference
+// re-casts every weight on every forward: autocast_mode.h:824).
+template <typename T>
+__device__ __forceinline__ void w2_tile_store(void* tiles, int i, float w) {
+  const int co = i / 400, ci = (i / 25) % 16, tap = i % 25;
+  T* t = reinterpret_cast<T*>(tiles);
+  t[((tap * 2 + (ci >> 3)) * 32 + co) * 8 + (ci & 7)] = Cvt<T>::from_f(w);
+  t[12800 + (((24 - tap) * 4 + (co >> 3)) * 16 + ci) * 8 + (co & 7)] = Cvt<T>::from_f(w);
+}
+
+// Sum the conv2 weight-gradient partial rows (one per wgrad CTA) in fixed row order, spread
+// over many SMs; runs on a side branch of the step graph, off the critical path, so that the
+// 8-CTA tail kernel reads one row instead of pulling rows x 51 KB through 8 SMs' L2 ports.
+__global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ gpart, float* __restrict__ gred, int rows) {
+  const int i = (blockIdx.x * 128 + threadIdx.x) * 4;
+  if (i >= 12800) return;
+  const float* p = gpart + OFF_W2 + i;
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+  for (int r = 0; r < rows; ++r) {
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(p + (size_t)r * N_PAD));
+    g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+  }
+  *reinterpret_cast<float4*>(gred + OFF_W2 + i) = g;
+}
+
+template <typename T>
+__global__ void k_refresh_w2_tiles(const float* params, void* tiles) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 12800) w2_tile_store<T>(tiles, i, params[OFF_W2 + i]);
+}
 
 template <typename T>
 __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS) k_step(StepArgs a) {
@@ -64,7 +102,8 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     else rows = a.rows_fc;
     if (round_t) {
       const float* p = a.gpart + e;
-#pragma unroll 4
+      if (a.gred != nullptr && e >= OFF_W2 && e < OFF_B2) { p = a.gred + e; rows = 1; }
+#pragma unroll 8
       for (int r = 0; r < rows; ++r) {
         const float4 v = __ldcg(reinterpret_cast<const float4*>(p + (size_t)r * N_PAD));
         g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
@@ -118,6 +157,15 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     const bool bad = !(isfinite(u.x) && isfinite(u.y) && isfinite(u.z) && isfinite(u.w));
     if (valid && bad) atomicOr(&s_nonfinite, 1);
   }
+  // ---- 4. cluster-wide found_inf through distributed shared memory
+  cluster.sync();
+  int found = 0;
+#pragma unroll
+  for (int r = 0; r < STEP_CTAS; ++r) found |= *cluster.map_shared_rank(&s_nonfinite, r);
+  cluster.sync();  // nobody may exit (and release its smem) before every CTA has read it
+
+  // the gradient taps are stored only now: a release at cluster scope waits for every global
+  // store issued before it, so none may be in flight while the two barriers above run
   if (valid) {
     if (e + 4 <= N_PARAM) {
       *reinterpret_cast<float4*>(a.grads_scaled + e) = tot;
@@ -128,13 +176,6 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     }
   }
 
-  // ---- 4. cluster-wide found_inf through distributed shared memory
-  cluster.sync();
-  int found = 0;
-#pragma unroll
-  for (int r = 0; r < STEP_CTAS; ++r) found |= *cluster.map_shared_rank(&s_nonfinite, r);
-  cluster.sync();  // nobody may exit (and release its smem) before every CTA has read it
-
   // ---- 5. SGD (skipped on overflow), same expression as _foreach_add_(p, g, alpha=-lr)
   if (valid && !found) {
     if (e + 4 <= N_PARAM) {
@@ -142,6 +183,11 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
       p.x = fmaf(-a.lr, u.x, p.x); p.y = fmaf(-a.lr, u.y, p.y);
       p.z = fmaf(-a.lr, u.z, p.z); p.w = fmaf(-a.lr, u.w, p.w);
       *reinterpret_cast<float4*>(a.params + e) = p;
+      if (sizeof(T) == 2 && a.w2_tiles != nullptr && e >= OFF_W2 && e < OFF_B2) {
+        const float pv[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w2_tile_store<T>(a.w2_tiles, e - OFF_W2 + j, pv[j]);
+      }
     } else {
       a.params[e] = fmaf(-a.lr, u.x, a.params[e]);
       a.params[e + 1] = fmaf(-a.lr, u.y, a.params[e + 1]);

@@ -180,10 +180,14 @@ class Engine:
 
     def profile_step(self, x: torch.Tensor, y: torch.Tensor, in_graph: bool = True):
         """One training step with per-kernel device timing: {kernel name: ms}."""
-        ms = (C.c_float * 13)()
+        ms = (C.c_float * 16)()
         self._check(self.lib.ddpstep_profile_step(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0], int(in_graph),
-                                                  ms, 13, self._stream()))
-        return {self.lib.ddpstep_kernel_name(i).decode(): float(ms[i]) for i in range(13)}
+                                                  ms, 16, self._stream()))
+        out, i = {}, 0
+        while self.lib.ddpstep_kernel_name(i):
+            out[self.lib.ddpstep_kernel_name(i).decode()] = float(ms[i])
+            i += 1
+        return out
 
     def launch_count(self) -> int:
         return int(self.lib.ddpstep_launch_count(self.ctx))

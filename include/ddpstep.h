@@ -132,13 +132,14 @@ int ddpstep_read_counts(ddpstep_ctx* ctx, float* correct, float* size, void* str
  * 4 dlogits, 5 d(conv2 out), 6 d(pool1 out).  Copies min(bytes, size) to host.             */
 int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* host, int64_t bytes);
 /* Profiling aid for bench.py: run ONE training step (state advances like any step) with a
- * CUDA event after each of its 13 kernels and return the 13 device durations in ms.
+ * CUDA event after each of its kernels (ddpstep_kernel_name lists them; n_out >= 16 is always
+ * enough) and return their device durations in ms.
  * in_graph = 1 replays the step as a graph with event-record nodes between the kernel nodes
  * (what the hot path does), 0 launches eagerly.  No reference counterpart: the reference
  * has no per-kernel instrumentation.                                  */
 int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
                          int32_t in_graph, float* ms_out, int32_t n_out, void* stream);
-const char* ddpstep_kernel_name(int32_t i);   /* names of those 13 kernels, "" past the end */
+const char* ddpstep_kernel_name(int32_t i);   /* names of those kernels, "" past the end */
 /* conv1 (5x5, pad 2, 1->16 channels) plus the per-channel BatchNorm batch statistics of its
  * output, WITHOUT a context and without allocating anything.  No counterpart in the
  * reference: it exists for hosts that cannot call cudaMalloc when they need the result -- a
