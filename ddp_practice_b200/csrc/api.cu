@@ -61,7 +61,7 @@ struct ddpstep_ctx {
   // graphs, keyed by batch (train) / -batch (eval with labels) / -batch-100000 (eval, no labels)
   std::map<long, GraphEntry> graphs;
   cudaStream_t cap_stream = nullptr, side1 = nullptr, side2 = nullptr;
-  cudaEvent_t ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
+  cudaEvent_t ev_f0 = nullptr, ev_j0 = nullptr, ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
   float* gred = nullptr;
   int64_t launches = 0;
   int esize = 2;
@@ -154,7 +154,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side1, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side2, cudaStreamNonBlocking);
-  for (cudaEvent_t* ev : {&ctx->ev_f1, &ctx->ev_j1, &ctx->ev_f2, &ctx->ev_j2})
+  for (cudaEvent_t* ev : {&ctx->ev_f0, &ctx->ev_j0, &ctx->ev_f1, &ctx->ev_j1, &ctx->ev_f2, &ctx->ev_j2})
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
   // kernels that need more than 48 KB of dynamic shared memory
   const int smem_dgrad = (32 * 18 * C14_RS + 8 * 32 * 25) * 4;
@@ -202,7 +202,7 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
   if (ctx->side1) cudaStreamDestroy(ctx->side1);
   if (ctx->side2) cudaStreamDestroy(ctx->side2);
-  for (cudaEvent_t ev : {ctx->ev_f1, ctx->ev_j1, ctx->ev_f2, ctx->ev_j2}) if (ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : {ctx->ev_f0, ctx->ev_j0, ctx->ev_f1, ctx->ev_j1, ctx->ev_f2, ctx->ev_j2}) if (ev) cudaEventDestroy(ev);
   delete ctx;
   return 0;
 }
@@ -244,8 +244,8 @@ extern "C" int ddpstep_load_state(ddpstep_ctx* ctx, const float* params, const f
   int64_t z[2] = {0, 0};
   CK(cudaMemcpy(ctx->nbt, nbt ? nbt : z, 16, cudaMemcpyHostToDevice));
   if (ctx->use_tc) {
-    if (ctx->cfg.dtype == DDPSTEP_FP16) k_refresh_w2_tiles<__half><<<50, 256>>>(ctx->params, ctx->w2_tiles);
-    else k_refresh_w2_tiles<__nv_bfloat16><<<50, 256>>>(ctx->params, ctx->w2_tiles);
+    if (ctx->cfg.dtype == DDPSTEP_FP16) k_refresh_w2_tiles<__half><<<100, 256>>>(ctx->params, ctx->w2_tiles);
+    else k_refresh_w2_tiles<__nv_bfloat16><<<100, 256>>>(ctx->params, ctx->w2_tiles);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
   }
@@ -321,6 +321,19 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
     }
     c->launches++;
   };
+  // the two weight-gradient branches and the filter-tile refresh do not sit on the activation chain:
+  // they run on side streams (parallel branches of the captured graph)
+  const bool fork = !(rec && rec->events);  // per-kernel profiling keeps everything on one stream
+  cudaStream_t s1 = fork ? c->side1 : s, s2 = fork ? c->side2 : s;
+  // 0. conv2 filter -> tcgen05 B tiles (side branch, joins before conv2)
+  bool tiles = false;
+  if constexpr (!std::is_same<T, float>::value) tiles = c->use_tc;
+  if (tiles) {
+    if (fork) { cudaEventRecord(c->ev_f0, s); cudaStreamWaitEvent(s1, c->ev_f0, 0); }
+    if constexpr (!std::is_same<T, float>::value) k_refresh_w2_tiles<T><<<100, 256, 0, s1>>>(c->params, c->w2_tiles);
+    mark();
+    if (fork) cudaEventRecord(c->ev_j0, s1);
+  }
   // 1. conv1 + local BN1 statistics
   const int g1 = std::min(B, 296);
   Conv1Args a1{x, c->params, c->y1, c->part1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
@@ -336,6 +349,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {  // tcgen05 implicit GEMM on the padded planes written by kernel 2
       tc = true;
+      if (fork) cudaStreamWaitEvent(s, c->ev_j0, 0);
       Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
       k_conv2_tc<T, 0><<<g2, TC_THREADS, tc_smem_bytes(2), s>>>(t2);
     }
@@ -353,10 +367,6 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 6. fc weight/bias gradient partials
   const int nsf = clampi(cdiv(B, 8), 1, 40);
   FcWgradArgs fw{c->p2, c->dlogits, c->gpart, B, cdiv(B, nsf)};
-  // the two weight-gradient branches do not feed the activation-gradient chain: they run on side
-  // streams (parallel branches of the captured graph) and join right before the tail kernel
-  const bool fork = !(rec && rec->events);  // per-kernel profiling keeps everything on one stream
-  cudaStream_t s1 = fork ? c->side1 : s, s2 = fork ? c->side2 : s;
   if (fork) { cudaEventRecord(c->ev_f1, s); cudaStreamWaitEvent(s1, c->ev_f1, 0); }
   k_fc_wgrad<T><<<dim3(7, nsf), 224, 0, s1>>>(fw); mark();
   if (fork) cudaEventRecord(c->ev_j1, s1);
@@ -392,7 +402,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   if (rec) rec->a_c1w = cw;
   k_conv1_wgrad<T><<<dim3(gc1, 4), C1W_THREADS, 0, s>>>(cw); mark();
   // 13. Reducer all-reduce + GradScaler + SGD
-  StepArgs sa{c->params, c->w2_tiles, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->bnbuf, c->nbt, c->ds, c->comm, B,
+  StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->bnbuf, c->nbt, c->ds, c->comm, B,
               gc1, gw, ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   k_step<T><<<STEP_CTAS, STEP_THREADS, 0, s>>>(sa); mark();
@@ -416,6 +426,9 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
     }
     c->launches++;
   };
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c->use_tc) { k_refresh_w2_tiles<T><<<100, 256, 0, s>>>(c->params, c->w2_tiles); mark(); }
+  }
   Conv1Args a1{x, c->params, c->y1, nullptr, c->st, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
   k_conv1_fwd<T><<<dim3(std::min(B, 296), C1_GROUPS), C1_THREADS, 0, s>>>(a1); mark();
@@ -623,9 +636,9 @@ extern "C" int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* ho
   return 0;
 }
 
-constexpr int kTrainKernels = 14;
+constexpr int kTrainKernels = 15;
 static const char* const kTrainKernelNames[kTrainKernels] = {
-    "conv1_fwd", "bn1_relu_pool", "conv2_fwd", "bn2_relu_pool", "fc_ce", "fc_wgrad", "bn2_bwd_reduce",
+    "w2_tiles_refresh", "conv1_fwd", "bn1_relu_pool", "conv2_fwd", "bn2_relu_pool", "fc_ce", "fc_wgrad", "bn2_bwd_reduce",
     "bn2_bwd_apply", "conv2_wgrad", "conv2_wgrad_reduce", "conv2_dgrad", "bn1_bwd_reduce", "conv1_wgrad", "step"};
 
 extern "C" const char* ddpstep_kernel_name(int32_t i) { return (i >= 0 && i < kTrainKernels) ? kTrainKernelNames[i] : ""; }
@@ -634,7 +647,7 @@ extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int6
                                     float* ms_out, int32_t n_out, void* stream) {
   int rc = check_step_args(ctx, x, batch);
   if (rc) return rc;
-  if (!y || !ms_out || n_out < kTrainKernels) return fail(ctx, DDPSTEP_E_ARG, "need labels and room for 14 durations");
+  if (!y || !ms_out || n_out < kTrainKernels) return fail(ctx, DDPSTEP_E_ARG, "need labels and room for 15 durations");
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   std::vector<cudaEvent_t> evs;

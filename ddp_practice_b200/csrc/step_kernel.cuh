@@ -22,7 +22,6 @@ namespace cg = cooperative_groups;
 
 struct StepArgs {
   float* params;
-  void* w2_tiles;       // [2][25][1 KB] conv2 filter as UMMA B tiles (fwd, dgrad) in the autocast dtype; may be null
   float* grads;         // tap T-c
   float* grads_scaled;  // tap T-b
   const float* gpart;   // [rows][N_PAD]
@@ -42,18 +41,12 @@ struct StepArgs {
 
 // conv2's filter is kept, besides its fp32 master copy, as ready-made tcgen05 B operands
 // (conv2_tc.cuh): 25 taps x [K chunk][N row][8] in the autocast dtype, once for the forward
-// (N = co, K = ci) and once for the data gradient (N = ci, K = co, taps flipped).  The SGD
-// kernel refreshes them as it writes the updated weights, so the conv kernels fetch 25 KB
-// with a single TMA copy instead of converting weights on every launch (the reference
-// re-casts every weight on every forward: autocast_mode.h:824).
-template <typename T>
-__device__ __forceinline__ void w2_tile_store(void* tiles, int i, float w) {
-  const int co = i / 400, ci = (i / 25) % 16, tap = i % 25;
-  T* t = reinterpret_cast<T*>(tiles);
-  t[((tap * 2 + (ci >> 3)) * 32 + co) * 8 + (ci & 7)] = Cvt<T>::from_f(w);
-  t[12800 + (((24 - tap) * 4 + (co >> 3)) * 16 + ci) * 8 + (co & 7)] = Cvt<T>::from_f(w);
-}
-
+// (N = co, K = ci) and once for the data gradient (N = ci, K = co, taps flipped).  A small
+// kernel on a side branch at the head of every step graph rebuilds them from the fp32 weights
+// (parallel to conv1, off the critical path), so the conv kernels fetch their 25 KB with a
+// single TMA copy.  (The reference re-casts every weight on every forward: autocast_mode.h:824.)
+// Doing this from inside the SGD kernel was measured at +7 us: 25,600 scattered 2-byte stores
+// issued by 4 SMs.
 // Sum the conv2 weight-gradient partial rows (one per wgrad CTA) in fixed row order, spread
 // over many SMs; runs on a side branch of the step graph, off the critical path, so that the
 // 8-CTA tail kernel reads one row instead of pulling rows x 51 KB through 8 SMs' L2 ports.
@@ -71,9 +64,21 @@ __global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ g
 }
 
 template <typename T>
-__global__ void k_refresh_w2_tiles(const float* params, void* tiles) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < 12800) w2_tile_store<T>(tiles, i, params[OFF_W2 + i]);
+__global__ void __launch_bounds__(256) k_refresh_w2_tiles(const float* __restrict__ params, void* tiles) {
+  // one thread per tile element (gather from the 51 KB filter, coalesced 2-byte stores)
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= 25600) return;
+  const int k8 = i & 7;
+  float w;
+  if (i < 12800) {  // forward: [tap][ci/8][co][ci%8]
+    const int co = (i >> 3) & 31, kc = (i >> 8) & 1, tap = i >> 9;
+    w = params[OFF_W2 + (co * 16 + kc * 8 + k8) * 25 + tap];
+  } else {          // data gradient: [tap'][co/8][ci][co%8], tap' = 24 - tap
+    const int j = i - 12800;
+    const int ci = (j >> 3) & 15, kc = (j >> 7) & 3, tp = j >> 9;
+    w = params[OFF_W2 + ((kc * 8 + k8) * 16 + ci) * 25 + (24 - tp)];
+  }
+  reinterpret_cast<T*>(tiles)[i] = Cvt<T>::from_f(w);
 }
 
 template <typename T>
@@ -87,6 +92,12 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   const unsigned long long epoch = a.ds->epoch;
   const float scale = a.ds->scale;
   if (tid == 0) s_nonfinite = 0;
+  // parameters are fetched now, long before they are needed, so the load overlaps everything below
+  float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (valid) {
+    if (e + 4 <= N_PARAM) p4 = *reinterpret_cast<const float4*>(a.params + e);
+    else { p4.x = a.params[e]; p4.y = a.params[e + 1]; }
+  }
   __syncthreads();
 
   // ---- 1. finish the local gradient (fixed row order => deterministic)
@@ -178,19 +189,14 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
 
   // ---- 5. SGD (skipped on overflow), same expression as _foreach_add_(p, g, alpha=-lr)
   if (valid && !found) {
+    float4 p = p4;
+    p.x = fmaf(-a.lr, u.x, p.x); p.y = fmaf(-a.lr, u.y, p.y);
+    p.z = fmaf(-a.lr, u.z, p.z); p.w = fmaf(-a.lr, u.w, p.w);
     if (e + 4 <= N_PARAM) {
-      float4 p = *reinterpret_cast<const float4*>(a.params + e);
-      p.x = fmaf(-a.lr, u.x, p.x); p.y = fmaf(-a.lr, u.y, p.y);
-      p.z = fmaf(-a.lr, u.z, p.z); p.w = fmaf(-a.lr, u.w, p.w);
       *reinterpret_cast<float4*>(a.params + e) = p;
-      if (sizeof(T) == 2 && a.w2_tiles != nullptr && e >= OFF_W2 && e < OFF_B2) {
-        const float pv[4] = {p.x, p.y, p.z, p.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) w2_tile_store<T>(a.w2_tiles, e - OFF_W2 + j, pv[j]);
-      }
     } else {
-      a.params[e] = fmaf(-a.lr, u.x, a.params[e]);
-      a.params[e + 1] = fmaf(-a.lr, u.y, a.params[e + 1]);
+      a.params[e] = p.x;
+      a.params[e + 1] = p.y;
     }
   }
 
