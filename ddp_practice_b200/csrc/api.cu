@@ -49,7 +49,7 @@ struct ddpstep_ctx {
   void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
   void *p1h = nullptr, *dy2h = nullptr, *w2_tiles = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
-  bool use_tc = false;
+  bool use_tc = false, use_wgrad_tc = false;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   float* x_stage = nullptr;
   int64_t* y_stage = nullptr;
@@ -137,6 +137,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
+    const char* envw = getenv("DDPSTEP_WGRAD_TC");
+    ctx->use_wgrad_tc = ctx->use_tc && !(envw && envw[0] == '0');
   }
   if (ctx->use_tc) { A(p1h, B * 2 * PL_BYTES); A(dy2h, B * 4 * PL_BYTES); A(w2_tiles, 2 * TC_WBYTES); }
   A(sym, sizeof(SymRegion));
@@ -161,6 +163,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<float, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__half, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__nv_bfloat16, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
@@ -379,8 +383,20 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   const int gw = std::min(B, 37);
   Conv2WgradArgs w2{c->p1, c->dy2, c->gpart, B};
   if (fork) { cudaEventRecord(c->ev_f2, s); cudaStreamWaitEvent(s2, c->ev_f2, 0); }
-  k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s2>>>(w2); mark();
-  k_reduce_rows<<<25, 128, 0, s2>>>(c->gpart, c->gred, gw); mark();
+  int gw_rows = gw;
+  bool wtc = false;
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c->use_tc && c->use_wgrad_tc) {
+      wtc = true;
+      gw_rows = std::min(B, 148);
+      Conv2WgradTcArgs wa{c->dy2h, c->p1h, c->gpart, B};
+      // small batches: split the 5 kh taps over 5 CTAs per image so more SMs take part
+      k_conv2_wgrad_tc<T><<<dim3(gw_rows, B <= 64 ? 5 : 1), TC_THREADS, WG_SMEM_BYTES, s2>>>(wa);
+    }
+  }
+  if (!wtc) k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s2>>>(w2);
+  mark();
+  k_reduce_rows<<<25, 128, 0, s2>>>(c->gpart, c->gred, gw_rows); mark();
   if (fork) cudaEventRecord(c->ev_j2, s2);
   Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
   tc = false;
@@ -403,7 +419,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   k_conv1_wgrad<T><<<dim3(gc1, 4), C1W_THREADS, 0, s>>>(cw); mark();
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->bnbuf, c->nbt, c->ds, c->comm, B,
-              gc1, gw, ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
+              gc1, gw_rows, ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   k_step<T><<<STEP_CTAS, STEP_THREADS, 0, s>>>(sa); mark();
   return cudaGetLastError();

@@ -283,4 +283,132 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
   }
 }
 
+
+// =======================================================================================
+// conv2 weight gradient on tcgen05:
+//     dW2[co][ci][kh][kw] = sum_{n, pixels q} dy2[n][q][co] * p1[n][q + (kh-2)*16 + (kw-2)][ci]
+// The reduction runs over pixels, so both operands are used MN-major (the 16-byte unit of the
+// padded-plane layout = 8 channels of one pixel = 8 consecutive M resp. N elements; consecutive
+// pixels = consecutive K):
+//   A = p1 plane c8  M = (shift j, ci%8): M-unit j is the SAME plane moved by j pixels -- a stride of
+//                    one 16-byte unit between M-units, i.e. overlapping core matrices.  M = 128 gives
+//                    16 shifts; j = 0..4 are the five kw taps, the other accumulator rows are never read.
+//   B = dy2 planes   N = co = 32 (4 units, one per plane)
+// One accumulator [128 x 32] per (kh, c8), kept in TMEM across ALL images of the CTA; 14 K-steps of
+// 16 pixels cover the 224-pixel output raster (its two pad columns hold zeros in dy2).  140 MMAs per
+// image; one epilogue per CTA writes one partial row.  gridDim.y = 5 splits the kh taps over 5 CTAs
+// (small batches: more SMs, 64 TMEM columns each); gridDim.y = 1 keeps all ten accumulators (320
+// columns) in one CTA (large batches: every image is fetched once).
+struct Conv2WgradTcArgs {
+  const void* dy2h;  // [B][4][320][8]
+  const void* p1h;   // [B][2][320][8]
+  float* gpart;      // [rows = gridDim.x][N_PAD]
+  int B;
+};
+
+constexpr int WG_DY_STAGE = 4 * PL_BYTES, WG_P_STAGE = 2 * PL_BYTES;
+constexpr int WG_BAR_OFF = 2 * WG_DY_STAGE + 2 * WG_P_STAGE + 1024;   // 1 KB slack: shifts read past the last p plane
+constexpr int WG_SMEM_BYTES = WG_BAR_OFF + 256;
+
+// MN-major operands: bits 15 / 16 of the instruction descriptor; in the shared-memory descriptor
+// LBO = stride between groups of 8 K, SBO = stride between 16-byte units along M/N
+// (cute::UMMA::make_umma_desc<Major::MN>)
+template <typename T> __device__ __forceinline__ uint32_t umma_idesc_mn(int n) {
+  return umma_idesc<T>(n) | (1u << 15) | (1u << 16);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcArgs a) {
+  extern __shared__ __align__(128) unsigned char wg_smem[];
+  unsigned char* dy_s = wg_smem;                         // [2][4 planes]
+  unsigned char* p_s = wg_smem + 2 * WG_DY_STAGE;        // [2][2 planes] + slack
+  uint64_t* bars = reinterpret_cast<uint64_t*>(wg_smem + WG_BAR_OFF);
+  uint64_t *full = bars, *empty = bars + 2, *done = bars + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int kh_lo = gridDim.y == 1 ? 0 : (int)blockIdx.y, kh_n = gridDim.y == 1 ? 5 : 1;
+  const uint32_t tmem_cols = gridDim.y == 1 ? 512u : 64u;
+  for (int i = tid; i < 256; i += TC_THREADS) reinterpret_cast<uint32_t*>(p_s + 2 * WG_P_STAGE)[i] = 0u;
+  if (tid == 0) {
+    for (int s = 0; s < 2; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int n_img = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const unsigned char* gdy = reinterpret_cast<const unsigned char*>(a.dy2h);
+  const unsigned char* gp = reinterpret_cast<const unsigned char*>(a.p1h);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int i = 0; i < n_img; ++i) {
+        const int s = i & 1;
+        mbar_wait(&empty[s], ((i >> 1) & 1) ^ 1);
+        mbar_expect_tx(&full[s], WG_DY_STAGE + WG_P_STAGE);
+        const int n = blockIdx.x + i * gridDim.x;
+        tma_bulk_g2s(dy_s + s * WG_DY_STAGE, gdy + (size_t)n * WG_DY_STAGE, WG_DY_STAGE, &full[s]);
+        tma_bulk_g2s(p_s + s * WG_P_STAGE, gp + (size_t)n * WG_P_STAGE, WG_P_STAGE, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_mn<T>(32);
+      for (int i = 0; i < n_img; ++i) {
+        const int s = i & 1;
+        mbar_wait(&full[s], (i >> 1) & 1);
+        tc_fence_after();
+        const uint32_t dy_addr = smem_u32(dy_s + s * WG_DY_STAGE), p_addr = smem_u32(p_s + s * WG_P_STAGE);
+#pragma unroll 1
+        for (int k = 0; k < kh_n; ++k) {
+          const int kh = kh_lo + k;
+#pragma unroll
+          for (int c8 = 0; c8 < 2; ++c8) {
+            const uint32_t d = tmem_base + (uint32_t)((k * 2 + c8) * 32);
+#pragma unroll 1
+            for (int t = 0; t < 14; ++t) {
+              const uint32_t q = 48 + 16 * t;  // first output pixel (plane raster index) of this K-step
+              const uint64_t ad = umma_desc(p_addr + c8 * PL_BYTES + (q + (kh - 2) * 16 - 2) * 16, 128, 16);
+              const uint64_t bd = umma_desc(dy_addr + q * 16, 128, PL_BYTES);
+              umma_f16(d, ad, bd, idesc, (i | t) != 0);
+            }
+          }
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(done);
+    }
+  } else if ((warp & 3) < 2) {
+    // epilogue: accumulator row m = kw*8 + ci%8 (m < 40: TMEM lanes 0..39), column = co
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const int q = warp & 3, m = q * 32 + lane, kw = m >> 3;
+    float* row = a.gpart + (size_t)blockIdx.x * N_PAD;
+#pragma unroll 1
+    for (int acc = 0; acc < 2 * kh_n; ++acc) {
+      const int kh = kh_lo + (acc >> 1), ci = (acc & 1) * 8 + (m & 7);
+      float v[32];
+      tmem_ld_row<32>(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * 32), v);
+      if (kw < 5) {
+#pragma unroll
+        for (int co = 0; co < 32; ++co) row[OFF_W2 + (co * 16 + ci) * 25 + kh * 5 + kw] = v[co];
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+  }
+}
+
 }  // namespace dstep
