@@ -193,18 +193,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
         mbar_wait(&tempty[s], ph ^ 1);
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(in_s + s * STAGE);
-#pragma unroll 1
+        // descriptors differ from a per-image base only by compile-time constants: the whole tap loop is
+        // unrolled so each MMA costs one 64-bit add per operand (a div/mod per tap made the single issuing
+        // thread, not the tensor core, the bottleneck: measured ~160 cycles per MMA)
+        const uint64_t ad0 = umma_desc(smem_u32(in_s + s * STAGE), PL_BYTES, 128);
+        const uint64_t bd0 = umma_desc(w_addr, N * 16, 128);
+#pragma unroll
         for (int tile = 0; tile < 2; ++tile) {
           const uint32_t d = tmem_base + (uint32_t)((s * 2 + tile) * N);
-#pragma unroll 1
+#pragma unroll
           for (int tap = 0; tap < 25; ++tap) {
             const int kh = tap / 5, kw = tap % 5;
             const uint32_t shift = (uint32_t)(tile * 128 + 16 * (kh + 1) + kw - 2) * 16u;
 #pragma unroll
             for (int kk = 0; kk < KSTEPS; ++kk) {
-              const uint64_t ad = umma_desc(a_addr + shift + kk * 2 * PL_BYTES, PL_BYTES, 128);
-              const uint64_t bd = umma_desc(w_addr + tap * 1024 + kk * 2 * N * 16, N * 16, 128);
+              const uint64_t ad = ad0 + (uint64_t)((shift + kk * 2 * PL_BYTES) >> 4);
+              const uint64_t bd = bd0 + (uint64_t)((tap * 1024 + kk * 2 * N * 16) >> 4);
               umma_f16(d, ad, bd, idesc, (tap | kk) != 0);
             }
           }
@@ -366,18 +370,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
         const int s = i & 1;
         mbar_wait(&full[s], (i >> 1) & 1);
         tc_fence_after();
-        const uint32_t dy_addr = smem_u32(dy_s + s * WG_DY_STAGE), p_addr = smem_u32(p_s + s * WG_P_STAGE);
+        const uint64_t bd0 = umma_desc(smem_u32(dy_s + s * WG_DY_STAGE) + 48 * 16, 128, PL_BYTES);
 #pragma unroll 1
         for (int k = 0; k < kh_n; ++k) {
           const int kh = kh_lo + k;
+          // first output pixel of K-step t is plane raster index 48 + 16 t; the p1 operand starts (kh-2) rows
+          // and 2 pixels earlier; everything else is a compile-time constant added to the descriptor
+          const uint64_t ad0 = umma_desc(smem_u32(p_s + s * WG_P_STAGE) + (48 + (kh - 2) * 16 - 2) * 16, 128, 16);
 #pragma unroll
           for (int c8 = 0; c8 < 2; ++c8) {
             const uint32_t d = tmem_base + (uint32_t)((k * 2 + c8) * 32);
-#pragma unroll 1
+#pragma unroll
             for (int t = 0; t < 14; ++t) {
-              const uint32_t q = 48 + 16 * t;  // first output pixel (plane raster index) of this K-step
-              const uint64_t ad = umma_desc(p_addr + c8 * PL_BYTES + (q + (kh - 2) * 16 - 2) * 16, 128, 16);
-              const uint64_t bd = umma_desc(dy_addr + q * 16, 128, PL_BYTES);
+              const uint64_t ad = ad0 + (uint64_t)((c8 * PL_BYTES + t * 256) >> 4);
+              const uint64_t bd = bd0 + (uint64_t)((t * 256) >> 4);
               umma_f16(d, ad, bd, idesc, (i | t) != 0);
             }
           }
