@@ -340,28 +340,32 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   }
   // 1. conv1 + local BN1 statistics
   const int g1 = std::min(B, 296);
-  Conv1Args a1{x, c->params, c->y1, c->part1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+  // small grids: the BN kernels reduce the conv kernels' partial sums themselves (no last-CTA tail)
+  const int defer1 = g1 <= 64, defer2 = std::min(B, 148) <= 64;
+  Conv1Args a1{x, c->params, c->y1, c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
   k_conv1_fwd<T><<<dim3(g1, C1_GROUPS), C1_THREADS, 0, s>>>(a1); mark();
   // 2. BN1 + ReLU + pool
-  BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps};
+  BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps,
+                defer1 ? c->part1 : nullptr, g1};
   k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
   // 3. conv2 + local BN2 statistics
   const int g2 = std::min(B, 148);
-  Conv14Args a2{c->p1, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+  Conv14Args a2{c->p1, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   bool tc = false;
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {  // tcgen05 implicit GEMM on the padded planes written by kernel 2
       tc = true;
       if (fork) cudaStreamWaitEvent(s, c->ev_j0, 0);
-      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, c->part2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
       k_conv2_tc<T, 0><<<g2, TC_THREADS, tc_smem_bytes(2), s>>>(t2);
     }
   }
   if (!tc) k_conv14<T, 16, 32, 0><<<dim3(g2, 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2);
   mark();
   // 4. BN2 + ReLU + pool
-  BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps};
+  BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps,
+                defer2 ? c->part2 : nullptr, g2};
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
   // 5. Linear + CE + dlogits + d(pool2 out)
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, c->dlogits, c->dflat, c->nll, c->counts,
@@ -376,7 +380,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   if (fork) cudaEventRecord(c->ev_j1, s1);
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);
-  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
+  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, 1, ns2, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
   k_bn_bwd_reduce<T, 32, 14><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
   k_bn2_bwd_apply<T><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
   // 9. conv2 weight gradient partials, 10. conv2 data gradient
@@ -398,12 +402,12 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   mark();
   k_reduce_rows<<<25, 128, 0, s2>>>(c->gpart, c->gred, gw_rows); mark();
   if (fork) cudaEventRecord(c->ev_j2, s2);
-  Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
+  Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
   tc = false;
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {
       tc = true;
-      Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
+      Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
       k_conv2_tc<T, 2><<<std::min(B, 148), TC_THREADS, tc_smem_bytes(4), s>>>(t2);
     }
   }
@@ -411,7 +415,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   mark();
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
   const int ns1 = clampi(cdiv(B, 2), 1, 32);
-  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, nullptr, nullptr, c->gpart};
+  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, 1, ns1, nullptr, nullptr, c->gpart};
   k_bn_bwd_reduce<T, 16, 28><<<dim3(16, ns1), 256, 0, s>>>(r1); mark();
   const int gc1 = std::min(B, 148);
   Conv1WgradArgs cw{r1, x};
@@ -445,23 +449,23 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) { k_refresh_w2_tiles<T><<<100, 256, 0, s>>>(c->params, c->w2_tiles); mark(); }
   }
-  Conv1Args a1{x, c->params, c->y1, nullptr, c->st, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
+  Conv1Args a1{x, c->params, c->y1, nullptr, 0, c->st, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
   k_conv1_fwd<T><<<dim3(std::min(B, 296), C1_GROUPS), C1_THREADS, 0, s>>>(a1); mark();
-  BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, c->st, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 1, 0, cfg.bn_momentum, cfg.bn_eps};
+  BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, c->st, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 1, 0, cfg.bn_momentum, cfg.bn_eps, nullptr, 0};
   k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
-  Conv14Args a2{c->p1, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
+  Conv14Args a2{c->p1, c->params, c->y2, nullptr, 0, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
   bool tc = false;
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {
       tc = true;
-      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, nullptr, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
+      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, nullptr, 0, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
       k_conv2_tc<T, 0><<<std::min(B, 148), TC_THREADS, tc_smem_bytes(2), s>>>(t2);
     }
   }
   if (!tc) k_conv14<T, 16, 32, 0><<<dim3(std::min(B, 148), 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2);
   mark();
-  BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps};
+  BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps, nullptr, 0};
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1};
   if (rec) rec->a_fc = f;
@@ -782,7 +786,7 @@ extern "C" int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const floa
   CommDev comm;
   memset(&comm, 0, sizeof comm);
   comm.world = 1;
-  Conv1Args a{x_dev, params_dev, y1_dev, sc->part, &sc->st, &sc->ds, comm, batch, conv_bias_double_round, 0, bn_eps};
+  Conv1Args a{x_dev, params_dev, y1_dev, sc->part, 0, &sc->st, &sc->ds, comm, batch, conv_bias_double_round, 0, bn_eps};
   switch (dtype) {
     case DDPSTEP_FP32: k_conv1_fwd<float><<<dim3(batch, C1_GROUPS), C1_THREADS, 0, s>>>(a); break;
     case DDPSTEP_FP16: k_conv1_fwd<__half><<<dim3(batch, C1_GROUPS), C1_THREADS, 0, s>>>(a); break;
@@ -793,3 +797,10 @@ extern "C" int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const floa
   CK(cudaMemcpyAsync(stats_dev + 16, sc->st.linvstd, 16 * sizeof(float), cudaMemcpyDeviceToDevice, s));
   return 0;
 }
+
+#ifdef DDPSTEP_TRACE
+extern "C" int ddpstep_read_trace(unsigned long long* out64) {
+  cudaDeviceSynchronize();
+  return cudaMemcpyFromSymbol(out64, dstep::g_trace, 64 * 8) == cudaSuccess ? 0 : -2;
+}
+#endif

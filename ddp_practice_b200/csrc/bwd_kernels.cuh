@@ -80,6 +80,7 @@ struct BnBwdArgs {
   DevState* ds;
   CommDev comm;
   int B, per_split, layer, sync;
+  int defer, nsplit;  // defer = 1: pass 1 only writes bpart; the consumer of the sums reduces the nsplit rows
   // pass 2 only
   void* dy;           // [B,C,H,H] gradient at the conv output
   void* dy_planes;    // optional second copy in the padded-plane layout (conv2_tc.cuh), layer 2 only
@@ -121,6 +122,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
     for (int w = 0; w < 8; ++w) v += red[w][tid];
     a.bpart[((size_t)c * gridDim.y + blockIdx.y) * 2 + tid] = v;
   }
+  if (a.defer) return;
   if (last_cta_done(&a.ds->ticket[2 + a.layer], gridDim.x * gridDim.y)) {
     const bool xchg = a.sync && a.comm.world > 1;
     if (tid < C) {
@@ -156,8 +158,42 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
 // k2 = invstd^2 * sum_dy_xmu / N  (`batch_norm_backward_elemt`, _functions.py:170).
 template <int C>
 __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
+  constexpr int OFF_G = (C == 16) ? OFF_G1 : OFF_G2, OFF_BE = (C == 16) ? OFF_BE1 : OFF_BE2;
+  __shared__ float s_loc[2 * C];
   const int c = threadIdx.x;
   const bool xchg = a.sync && a.comm.world > 1;
+  const bool first = blockIdx.x == 0 && blockIdx.y == 0;
+  if (a.defer) {
+    // this rank's sums from the pass-1 partials (thread = (channel, which sum)); CTA (0,0) also
+    // publishes d(gamma), d(beta) and, under SyncBN, pushes the sums to every rank
+    if (c < 2 * C) {
+      const int ch = c >> 1, which = c & 1;
+      double acc = 0.0;
+#pragma unroll 8
+      for (int sp = 0; sp < a.nsplit; ++sp) acc += (double)__ldcg(&a.bpart[((size_t)ch * a.nsplit + sp) * 2 + which]);
+      s_loc[which * C + ch] = (float)acc;
+    }
+    __syncthreads();
+    if (first) {
+      if (c < C) {
+        a.gdirect[OFF_G + c] = s_loc[C + c] * a.st->invstd[c];  // d(gamma), local: DDP averages it
+        a.gdirect[OFF_BE + c] = s_loc[c];                        // d(beta)
+        if (xchg) {
+          for (int q = 0; q < a.comm.world; ++q) {
+            float* slot = a.comm.peer[q]->slot_bn_bwd[a.layer][a.comm.rank];
+            slot[c] = s_loc[c];
+            slot[C + c] = s_loc[C + c];
+          }
+        }
+      }
+      if (xchg) {
+        __threadfence_system();
+        __syncthreads();
+        if (c < a.comm.world)
+          st_release_sys(&a.comm.peer[c]->flag_bn[2 + (1 - a.layer)][a.comm.rank], a.ds->epoch + 1ull);
+      }
+    }
+  }
   if (xchg) {
     if (c < a.comm.world)
       wait_flag(&a.comm.self->flag_bn[2 + (1 - a.layer)][c], a.ds->epoch + 1ull, &a.ds->error);
@@ -172,6 +208,9 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
         s0 += __ldcg(&slot[c]);
         s1 += __ldcg(&slot[C + c]);
       }
+    } else if (a.defer) {
+      s0 = s_loc[c];
+      s1 = s_loc[C + c];
     } else {
       s0 = a.st->lsum_dy[c];
       s1 = a.st->lsum_dy_xmu[c];

@@ -137,4 +137,20 @@ __device__ __forceinline__ bool last_cta_done(unsigned int* ticket, unsigned int
   return s_last != 0;
 }
 
+// Optional in-kernel phase timestamps (build with -DDDPSTEP_TRACE): CTA 0 writes globaltimer values
+// into a small global buffer so latency chains inside a kernel can be read off directly.
+#ifdef DDPSTEP_TRACE
+__device__ unsigned long long g_trace[64];
+__device__ __forceinline__ void trace_mark(int slot) {
+  if (blockIdx.x == 0 && blockIdx.y == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_trace[slot] = t;
+  }
+}
+#define TRACE(slot) trace_mark(slot)
+#else
+#define TRACE(slot)
+#endif
+
 }  // namespace dstep

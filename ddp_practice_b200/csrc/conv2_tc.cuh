@@ -109,12 +109,30 @@ template <> __device__ __forceinline__ void tmem_ld_row<32>(uint32_t taddr, floa
   tmem_ld_row<16>(taddr + 16, v + 16);
 }
 
+// Sum v[c] over the 32 lanes of a warp for all 32 channels c at once; lane l returns channel l's
+// total.  31 shuffles instead of 32 x 5: at every step a lane keeps the half of its values whose
+// index bit matches its lane bit and trades the other half with its partner.  Fixed order.
+__device__ __forceinline__ float warp_transpose_sum32(float* v, int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float keep = up ? v[i + off] : v[i];
+      const float send = up ? v[i] : v[i + off];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
 struct Conv2TcArgs {
   const void* wtiles;  // [25][1 KB] B operand tiles for this MODE (step_kernel.cuh: w2_tile_store)
   const void* in;      // padded planes: MODE 0 p1h [B][2][320][8], MODE 2 dy2h [B][4][320][8]
   const float* params;
   void* out;           // MODE 0 y2 [B,32,14,14], MODE 2 dp1 [B,16,14,14]  (NCHW, T)
   float* part;         // MODE 0: BN partial sums [gridDim.x][32][2] (nullptr in eval)
+  int defer;           // 1: the consumer reduces the partial rows (no last-CTA tail here)
   BnStat* st;
   DevState* ds;
   CommDev comm;
@@ -136,6 +154,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
   uint64_t *full = bars, *empty = bars + 2, *tfull = bars + 4, *tempty = bars + 6, *wbar = bars + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (MODE == 0 && tid == 0) TRACE(0);
 
   // ---- one-time setup: barriers, TMEM, and the 25 filter taps (ready-made K-major B tiles kept
   // up to date by the SGD kernel) fetched with one TMA copy
@@ -167,6 +186,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (MODE == 0 && tid == 0) TRACE(1);
   const int n_img = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // images of this CTA
   const unsigned char* gin = reinterpret_cast<const unsigned char*>(a.in);
 
@@ -187,11 +207,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       const uint32_t idesc = umma_idesc<T>(N);
       const uint32_t w_addr = smem_u32(w_s);
       mbar_wait(wbar, 0);
+      if (MODE == 0) TRACE(2);
       for (int i = 0; i < n_img; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;
         mbar_wait(&tempty[s], ph ^ 1);
         mbar_wait(&full[s], ph);
+        if (MODE == 0) TRACE(3);
         tc_fence_after();
         // descriptors differ from a per-image base only by compile-time constants: the whole tap loop is
         // unrolled so each MMA costs one 64-bit add per operand (a div/mod per tap made the single issuing
@@ -213,6 +235,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
             }
           }
         }
+        if (MODE == 0) TRACE(4);
         umma_commit(&empty[s]);   // smem stage may be refilled
         umma_commit(&tfull[s]);   // accumulators ready
       }
@@ -232,6 +255,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       const int s = i & 1;
       const int n = blockIdx.x + i * gridDim.x;
       mbar_wait(&tfull[s], (i >> 1) & 1);
+      if (MODE == 0 && tid == 64) TRACE(5);
       tc_fence_after();
 #pragma unroll 1
       for (int tile = 0; tile < 2; ++tile) {
@@ -255,16 +279,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       }
       tc_fence_before();
       mbar_arrive(&tempty[s]);
+      if (MODE == 0 && tid == 64) TRACE(6);
     }
     if (MODE == 0 && a.part != nullptr) {
       // deterministic CTA reduction of the per-thread statistics: butterfly inside the warp, then
       // the four epilogue warps are summed in a fixed order below
       float* red = reinterpret_cast<float*>(in_s);  // [4 warps][64]; the image stages are idle by now
-#pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        const float t0 = warp_sum(s_sum[c]), t1 = warp_sum(s_sq[c]);
-        if (lane == 0) { red[q * 64 + c] = t0; red[q * 64 + 32 + c] = t1; }
-      }
+      const float t0 = warp_transpose_sum32(s_sum, lane), t1 = warp_transpose_sum32(s_sq, lane);
+      red[q * 64 + lane] = t0;        // lane l ends up with channel l
+      red[q * 64 + 32 + lane] = t1;
     }
   }
   tc_fence_before();
@@ -277,14 +300,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       a.part[((size_t)blockIdx.x * 32 + c) * 2 + stat] = acc;
     }
   }
+  if (MODE == 0 && tid == 0) TRACE(7);
   if (warp == 0) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
   }
   if (MODE == 0 && a.part != nullptr) {
-    if (last_cta_done(&a.ds->ticket[1], gridDim.x))
+    if (!a.defer && last_cta_done(&a.ds->ticket[1], gridDim.x))
       finalize_fwd_stats<32>(a.part, gridDim.x, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
   }
+  if (MODE == 0 && tid == 0) TRACE(8);
 }
 
 

@@ -114,6 +114,7 @@ struct Conv1Args {
   const float* params;
   void* y1;
   float* part;  // [gridDim.x][16][2]
+  int defer;    // 1: leave the partial sums to the consumer (bn_forward_stats), no last-CTA finalisation
   BnStat* st;
   DevState* ds;
   CommDev comm;
@@ -218,6 +219,7 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
     const float v = ((red[0][tid] + red[1][tid]) + red[2][tid]) + red[3][tid];
     a.part[((size_t)blockIdx.x * 16 + cg * 4 + j) * 2 + stat] = v;
   }
+  if (a.defer) return;
   if (last_cta_done(&a.ds->ticket[0], gridDim.x * gridDim.y))
     finalize_fwd_stats<16>(a.part, gridDim.x, (float)a.B * 784.f, a.eps, a.st, 0, a.comm, a.ds, a.sync);
 }
@@ -239,6 +241,11 @@ struct BnPoolArgs {
   CommDev comm;
   int B, layer, eval, sync;
   float momentum, eps;
+  // deferred finalisation (small grids): the conv kernel only wrote its per-CTA partial sums and
+  // THIS kernel's CTAs reduce them in their prologue -- no fence / ticket / serial last-CTA tail in
+  // the producer.  part == nullptr: the producer finalised (large grids) and st->l* are valid.
+  const float* part;
+  int rows;
 };
 
 template <int C>
@@ -246,6 +253,49 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
                                  float local_count) {
   const int c = threadIdx.x;
   const bool xchg = !a.eval && a.sync && a.comm.world > 1;
+  const bool defer = !a.eval && a.part != nullptr;
+  float lmean = 0.f, linvstd = 0.f, lvar_unb = 0.f;
+  if (defer) {
+    // local statistics from the partial rows: column = (channel, stat), several row lanes per column
+    __shared__ double fin[512];
+    constexpr int COLS = 2 * C;
+    const int lanes = min((int)blockDim.x / COLS, 512 / COLS);
+    const int col = c % COLS, lane = c / COLS;
+    if (lane < lanes) {
+      double acc = 0.0;
+#pragma unroll 4
+      for (int r = lane; r < a.rows; r += lanes) acc += (double)__ldcg(&a.part[(size_t)r * COLS + col]);
+      fin[lane * COLS + col] = acc;
+    }
+    __syncthreads();
+    if (c < C) {
+      double sm = 0.0, sq = 0.0;
+      for (int l = 0; l < lanes; ++l) { sm += fin[l * COLS + 2 * c]; sq += fin[l * COLS + 2 * c + 1]; }
+      const double mean = sm / (double)local_count;
+      double var = sq / (double)local_count - mean * mean;
+      if (var < 0.0) var = 0.0;
+      lmean = (float)mean;
+      linvstd = (float)(1.0 / sqrt(var + (double)a.eps));
+      lvar_unb = (float)(var * ((double)local_count / ((double)local_count - 1.0)));
+      if (xchg && blockIdx.x == 0) {  // the all_gather of _functions.py:74, pushed by CTA 0
+        for (int q = 0; q < a.comm.world; ++q) {
+          float* slot = a.comm.peer[q]->slot_bn_fwd[a.layer][a.comm.rank];
+          slot[c] = lmean;
+          slot[C + c] = linvstd;
+          if (c == 0) slot[2 * C] = local_count;
+        }
+      }
+    }
+    if (xchg && blockIdx.x == 0) {
+      __threadfence_system();
+      __syncthreads();
+      if (c < a.comm.world) st_release_sys(&a.comm.peer[c]->flag_bn[a.layer][a.comm.rank], a.ds->epoch + 1ull);
+    }
+  } else if (!a.eval && c < C) {
+    lmean = a.st->lmean[c];
+    linvstd = a.st->linvstd[c];
+    lvar_unb = a.st->lvar_unbiased[c];
+  }
   if (xchg) {
     if (c < a.comm.world) wait_flag(&a.comm.self->flag_bn[a.layer][c], a.ds->epoch + 1ull, &a.ds->error);
     __syncthreads();
@@ -273,9 +323,9 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
       var_unb = m2 / (n - 1.0f);
       n_total = n;
     } else {
-      mean = a.st->lmean[c];
-      invstd = a.st->linvstd[c];
-      var_unb = a.st->lvar_unbiased[c];
+      mean = lmean;
+      invstd = linvstd;
+      var_unb = lvar_unb;
     }
     s_mean[c] = mean;
     s_invstd[c] = invstd;
@@ -339,6 +389,7 @@ struct Conv14Args {
   const float* params;
   void* out;
   float* part;  // MODE 0: [gridDim.x][32][2]
+  int defer;
   BnStat* st;
   DevState* ds;
   CommDev comm;
@@ -438,7 +489,7 @@ __global__ void __launch_bounds__(128) k_conv14(Conv14Args a) {
       for (int i = 0; i < 14; ++i) v += red[cl * 14 + i][stat];
       a.part[((size_t)blockIdx.x * 32 + cog * 8 + cl) * 2 + stat] = v;
     }
-    if (last_cta_done(&a.ds->ticket[1], gridDim.x * gridDim.y))
+    if (!a.defer && last_cta_done(&a.ds->ticket[1], gridDim.x * gridDim.y))
       finalize_fwd_stats<32>(a.part, gridDim.x, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
   }
 }
