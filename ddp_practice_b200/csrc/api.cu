@@ -49,7 +49,7 @@ struct ddpstep_ctx {
   void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
   void *p1h = nullptr, *dy2h = nullptr, *w2_tiles = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
-  bool use_tc = false, use_wgrad_tc = false;
+  bool use_tc = false, use_wgrad_tc = false, use_pdl = true;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   float* x_stage = nullptr;
   int64_t* y_stage = nullptr;
@@ -137,6 +137,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
+    const char* envp = getenv("DDPSTEP_PDL");
+    ctx->use_pdl = !(envp && envp[0] == '0');
     const char* envw = getenv("DDPSTEP_WGRAD_TC");
     ctx->use_wgrad_tc = ctx->use_tc && !(envw && envw[0] == '0');
   }
@@ -306,6 +308,19 @@ struct Recorder {  // keeps the argument structs that hold x / y so graph replay
   Conv1WgradArgs a_c1w;
 };
 
+// Kernel launch with an optional programmatic (PDL) edge to the previous kernel of the stream:
+// the kernel may start while its predecessor is still running and orders itself with pdl_wait().
+template <typename A>
+static void launch_k(void (*kernel)(A), dim3 grid, dim3 block, size_t smem, cudaStream_t s, const A& args, bool pdl) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, args);
+}
+
 template <typename T>
 static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
   const ddpstep_config& cfg = c->cfg;
@@ -328,6 +343,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // the two weight-gradient branches and the filter-tile refresh do not sit on the activation chain:
   // they run on side streams (parallel branches of the captured graph)
   const bool fork = !(rec && rec->events);  // per-kernel profiling keeps everything on one stream
+  const bool pdl = fork && c->use_pdl;
   cudaStream_t s1 = fork ? c->side1 : s, s2 = fork ? c->side2 : s;
   // 0. conv2 filter -> tcgen05 B tiles (side branch, joins before conv2)
   bool tiles = false;
@@ -348,7 +364,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 2. BN1 + ReLU + pool
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps,
                 defer1 ? c->part1 : nullptr, g1};
-  k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
+  launch_k(k_bn_relu_pool<T, 16, 28>, dim3(clampi(cdiv(B * 16 * 196, 256), 1, 1184)), dim3(256), 0, s, b1, pdl); mark();
   // 3. conv2 + local BN2 statistics
   const int g2 = std::min(B, 148);
   Conv14Args a2{c->p1, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
@@ -358,7 +374,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
       tc = true;
       if (fork) cudaStreamWaitEvent(s, c->ev_j0, 0);
       Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
-      k_conv2_tc<T, 0><<<g2, TC_THREADS, tc_smem_bytes(2), s>>>(t2);
+      launch_k(k_conv2_tc<T, 0>, dim3(g2), dim3(TC_THREADS), tc_smem_bytes(2), s, t2, pdl);
     }
   }
   if (!tc) k_conv14<T, 16, 32, 0><<<dim3(g2, 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2);
@@ -366,12 +382,12 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 4. BN2 + ReLU + pool
   BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps,
                 defer2 ? c->part2 : nullptr, g2};
-  k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
+  launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark();
   // 5. Linear + CE + dlogits + d(pool2 out)
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, c->dlogits, c->dflat, c->nll, c->counts,
            c->ds, B, cfg.use_scaler, 0};
   if (rec) rec->a_fc = f;
-  k_fc_ce<T><<<std::min(B, 296), 224, 0, s>>>(f); mark();
+  launch_k(k_fc_ce<T>, dim3(std::min(B, 296)), dim3(224), 0, s, f, pdl); mark();
   // 6. fc weight/bias gradient partials
   const int nsf = clampi(cdiv(B, 8), 1, 40);
   FcWgradArgs fw{c->p2, c->dlogits, c->gpart, B, cdiv(B, nsf)};
@@ -381,12 +397,25 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);
   BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, 1, ns2, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
-  k_bn_bwd_reduce<T, 32, 14><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
-  k_bn2_bwd_apply<T><<<dim3(32, ns2), 256, 0, s>>>(r2); mark();
+  launch_k(k_bn_bwd_reduce<T, 32, 14>, dim3(32, ns2), dim3(256), 0, s, r2, pdl); mark();
+  launch_k(k_bn2_bwd_apply<T>, dim3(32, ns2), dim3(256), 0, s, r2, pdl); mark();
   // 9. conv2 weight gradient partials, 10. conv2 data gradient
   const int gw = std::min(B, 37);
   Conv2WgradArgs w2{c->p1, c->dy2, c->gpart, B};
-  if (fork) { cudaEventRecord(c->ev_f2, s); cudaStreamWaitEvent(s2, c->ev_f2, 0); }
+  if (fork) cudaEventRecord(c->ev_f2, s);  // the weight-gradient branch forks here, but is enqueued after the
+  // data-gradient kernel below so that the critical-path kernel is dispatched first
+  Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
+  tc = false;
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c->use_tc) {
+      tc = true;
+      Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
+      launch_k(k_conv2_tc<T, 2>, dim3(std::min(B, 148)), dim3(TC_THREADS), tc_smem_bytes(4), s, t2, pdl);
+    }
+  }
+  if (!tc) k_conv14<T, 32, 16, 2><<<dim3(std::min(B, 296), 2), 128, (32 * 18 * C14_RS + 8 * 32 * 25) * 4, s>>>(d2);
+  mark();
+  if (fork) cudaStreamWaitEvent(s2, c->ev_f2, 0);
   int gw_rows = gw;
   bool wtc = false;
   if constexpr (!std::is_same<T, float>::value) {
@@ -402,30 +431,19 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   mark();
   k_reduce_rows<<<25, 128, 0, s2>>>(c->gpart, c->gred, gw_rows); mark();
   if (fork) cudaEventRecord(c->ev_j2, s2);
-  Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
-  tc = false;
-  if constexpr (!std::is_same<T, float>::value) {
-    if (c->use_tc) {
-      tc = true;
-      Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
-      k_conv2_tc<T, 2><<<std::min(B, 148), TC_THREADS, tc_smem_bytes(4), s>>>(t2);
-    }
-  }
-  if (!tc) k_conv14<T, 32, 16, 2><<<dim3(std::min(B, 296), 2), 128, (32 * 18 * C14_RS + 8 * 32 * 25) * 4, s>>>(d2);
-  mark();
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
   const int ns1 = clampi(cdiv(B, 2), 1, 32);
   BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, 1, ns1, nullptr, nullptr, c->gpart};
-  k_bn_bwd_reduce<T, 16, 28><<<dim3(16, ns1), 256, 0, s>>>(r1); mark();
+  launch_k(k_bn_bwd_reduce<T, 16, 28>, dim3(16, ns1), dim3(256), 0, s, r1, pdl); mark();
   const int gc1 = std::min(B, 148);
   Conv1WgradArgs cw{r1, x};
   if (rec) rec->a_c1w = cw;
-  k_conv1_wgrad<T><<<dim3(gc1, 4), C1W_THREADS, 0, s>>>(cw); mark();
+  launch_k(k_conv1_wgrad<T>, dim3(gc1, 4), dim3(C1W_THREADS), 0, s, cw, pdl); mark();
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->bnbuf, c->nbt, c->ds, c->comm, B,
               gc1, gw_rows, ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
-  k_step<T><<<STEP_CTAS, STEP_THREADS, 0, s>>>(sa); mark();
+  launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();
   return cudaGetLastError();
 }
 
@@ -659,7 +677,7 @@ extern "C" int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* ho
 constexpr int kTrainKernels = 15;
 static const char* const kTrainKernelNames[kTrainKernels] = {
     "w2_tiles_refresh", "conv1_fwd", "bn1_relu_pool", "conv2_fwd", "bn2_relu_pool", "fc_ce", "fc_wgrad", "bn2_bwd_reduce",
-    "bn2_bwd_apply", "conv2_wgrad", "conv2_wgrad_reduce", "conv2_dgrad", "bn1_bwd_reduce", "conv1_wgrad", "step"};
+    "bn2_bwd_apply", "conv2_dgrad", "conv2_wgrad", "conv2_wgrad_reduce", "bn1_bwd_reduce", "conv1_wgrad", "step"};
 
 extern "C" const char* ddpstep_kernel_name(int32_t i) { return (i >= 0 && i < kTrainKernels) ? kTrainKernelNames[i] : ""; }
 
@@ -801,6 +819,6 @@ extern "C" int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const floa
 #ifdef DDPSTEP_TRACE
 extern "C" int ddpstep_read_trace(unsigned long long* out64) {
   cudaDeviceSynchronize();
-  return cudaMemcpyFromSymbol(out64, dstep::g_trace, 64 * 8) == cudaSuccess ? 0 : -2;
+  return cudaMemcpyFromSymbol(out64, dstep::g_trace, 256 * 8) == cudaSuccess ? 0 : -2;
 }
 #endif

@@ -35,6 +35,7 @@ struct FcWgradArgs {
 
 template <typename T>
 __global__ void __launch_bounds__(224) k_fc_wgrad(FcWgradArgs a) {
+  if (threadIdx.x == 0) TRACE(6 * 16 + 0);
   __shared__ float dl_s[32][10];
   const int tid = threadIdx.x;
   const int k = blockIdx.x * 224 + tid;
@@ -89,6 +90,7 @@ struct BnBwdArgs {
 
 template <typename T, int C, int H>
 __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
+  if (threadIdx.x == 0) TRACE((C == 32 ? 7 : 11) * 16 + 0);
   constexpr int HP = H / 2;
   constexpr int OFF_G = (C == 16) ? OFF_G1 : OFF_G2, OFF_BE = (C == 16) ? OFF_BE1 : OFF_BE2;
   __shared__ float red[8][2];
@@ -97,6 +99,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
   const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G + c], b = a.params[OFF_BE + c];
+  pdl_sync();  // predecessor produced dpool; the statistics above come from an earlier kernel
   float sdy = 0.f, sdyx = 0.f;
   const int total = max(0, n1 - n0) * HP * HP;
   for (int e = tid; e < total; e += 256) {
@@ -163,20 +166,28 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
   const int c = threadIdx.x;
   const bool xchg = a.sync && a.comm.world > 1;
   const bool first = blockIdx.x == 0 && blockIdx.y == 0;
+  // issued first so that their latency hides behind the partial-sum loads below
+  float n_tot = 0.f, inv_c = 0.f;
+  if (c < C) { n_tot = a.st->n_total; inv_c = a.st->invstd[c]; }
+  pdl_sync();  // predecessor: pass 1 (bpart)
   if (a.defer) {
-    // this rank's sums from the pass-1 partials (thread = (channel, which sum)); CTA (0,0) also
-    // publishes d(gamma), d(beta) and, under SyncBN, pushes the sums to every rank
-    if (c < 2 * C) {
-      const int ch = c >> 1, which = c & 1;
+    // this rank's sums from the pass-1 partials: thread = (quarter of the rows, channel, which sum), so the
+    // loads overlap; quarters are combined in fixed order.  CTA (0,0) also publishes d(gamma), d(beta) and,
+    // under SyncBN, pushes the sums to every rank
+    __shared__ float s_q[4][2 * C];
+    if (c < 8 * C) {
+      const int qd = c / (2 * C), ch = (c % (2 * C)) >> 1, which = c & 1;
       double acc = 0.0;
 #pragma unroll 8
-      for (int sp = 0; sp < a.nsplit; ++sp) acc += (double)__ldcg(&a.bpart[((size_t)ch * a.nsplit + sp) * 2 + which]);
-      s_loc[which * C + ch] = (float)acc;
+      for (int sp = qd; sp < a.nsplit; sp += 4) acc += (double)__ldcg(&a.bpart[((size_t)ch * a.nsplit + sp) * 2 + which]);
+      s_q[qd][which * C + ch] = (float)acc;
     }
+    __syncthreads();
+    if (c < 2 * C) s_loc[c] = ((s_q[0][c] + s_q[1][c]) + s_q[2][c]) + s_q[3][c];
     __syncthreads();
     if (first) {
       if (c < C) {
-        a.gdirect[OFF_G + c] = s_loc[C + c] * a.st->invstd[c];  // d(gamma), local: DDP averages it
+        a.gdirect[OFF_G + c] = s_loc[C + c] * inv_c;  // d(gamma), local: DDP averages it
         a.gdirect[OFF_BE + c] = s_loc[c];                        // d(beta)
         if (xchg) {
           for (int q = 0; q < a.comm.world; ++q) {
@@ -215,9 +226,8 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
       s0 = a.st->lsum_dy[c];
       s1 = a.st->lsum_dy_xmu[c];
     }
-    const float n = a.st->n_total, is = a.st->invstd[c];
-    s_k1[c] = s0 / n;
-    s_k2[c] = is * is * s1 / n;
+    s_k1[c] = s0 / n_tot;
+    s_k2[c] = inv_c * inv_c * s1 / n_tot;
   }
   __syncthreads();
 }
@@ -226,10 +236,12 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
 // wgrad); also the conv2 bias gradient partials (sum of the rounded values).  grid (32, NS).
 template <typename T>
 __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
+  if (threadIdx.x == 0) TRACE(9 * 16 + 0);
   constexpr int C = 32, H = 14, HP = 7;
   __shared__ float s_k1[C], s_k2[C];
   __shared__ float red[8];
   bn_backward_sums<C>(a, s_k1, s_k2);
+  if (threadIdx.x == 0) TRACE(9 * 16 + 1);
   const int tid = threadIdx.x, c = blockIdx.x;
   const int n0 = blockIdx.y * a.per_split, n1 = min(a.B, n0 + a.per_split);
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
@@ -262,6 +274,7 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
       stf<T>(pl, o[0]); stf<T>(pl + 8, o[1]); stf<T>(pl + 128, o[2]); stf<T>(pl + 136, o[3]);
     }
   }
+  if (threadIdx.x == 0) TRACE(9 * 16 + 2);
   bsum = warp_sum(bsum);
   if ((tid & 31) == 0) red[tid >> 5] = bsum;
   __syncthreads();
@@ -270,6 +283,7 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
     for (int w = 0; w < 8; ++w) v += red[w];
     a.gpart[(size_t)blockIdx.y * N_PAD + OFF_B2 + c] = v;
   }
+  if (threadIdx.x == 0) TRACE(9 * 16 + 15);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -351,12 +365,24 @@ constexpr int C1W_THREADS = 160;
 
 template <typename T>
 __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
+  if (threadIdx.x == 0) TRACE(12 * 16 + 0);
   __shared__ __align__(16) float dy_s[4 * 784];
   __shared__ __align__(16) float xs[32 * C1_XS];
   __shared__ float red[140][6];
   __shared__ float s_k1[16], s_k2[16];
-  bn_backward_sums<16>(a.bn, s_k1, s_k2);
+  __shared__ float s_cst[4][6];  // per channel of this CTA: mean, invstd, gamma, beta, k1, k2
   const int tid = threadIdx.x, cg = blockIdx.y;
+  float c_mu = 0.f, c_is = 0.f, c_g = 0.f, c_b = 0.f;
+  if (tid < 4) {  // fetched before the sums so the latencies overlap
+    const int c = cg * 4 + tid;
+    c_mu = a.bn.st->mean[c]; c_is = a.bn.st->invstd[c];
+    c_g = a.bn.params[OFF_G1 + c]; c_b = a.bn.params[OFF_BE1 + c];
+  }
+  bn_backward_sums<16>(a.bn, s_k1, s_k2);
+  if (tid < 4) {
+    s_cst[tid][0] = c_mu; s_cst[tid][1] = c_is; s_cst[tid][2] = c_g; s_cst[tid][3] = c_b;
+    s_cst[tid][4] = s_k1[cg * 4 + tid]; s_cst[tid][5] = s_k2[cg * 4 + tid];
+  }
   for (int i = tid; i < 32 * C1_XS; i += C1W_THREADS) xs[i] = 0.f;
   const T* __restrict__ y1 = reinterpret_cast<const T*>(a.bn.y);
   const T* __restrict__ dp1 = reinterpret_cast<const T*>(a.bn.dpool);
@@ -380,11 +406,11 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
         load2<T>(y1 + off, v[0], v[1]);
         load2<T>(y1 + off + 28, v[2], v[3]);
         const float dd = ldf<T>(&dp1[((size_t)n * 16 + c) * 196 + w]);
-        const float mu = a.bn.st->mean[c], is = a.bn.st->invstd[c], g = a.bn.params[OFF_G1 + c];
+        const float mu = s_cst[cl][0], is = s_cst[cl][1], g = s_cst[cl][2];
         bool live;
-        const int arg = pool_winner<T>(v, mu, is, g, a.bn.params[OFF_BE1 + c], live);
+        const int arg = pool_winner<T>(v, mu, is, g, s_cst[cl][3], live);
         const float d = live ? dd : 0.f;
-        const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
+        const float k1 = s_cst[cl][4], k2 = s_cst[cl][5], k3 = is * g;
         float* dst = dy_s + (cl * 28 + 2 * ph) * 28 + 2 * pw;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {

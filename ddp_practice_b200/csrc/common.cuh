@@ -115,6 +115,16 @@ __device__ __forceinline__ void wait_flag(const unsigned long long* flag, unsign
   }
 }
 
+// Programmatic dependent launch (PDL): inside the step graph a kernel may be launched while its
+// predecessor is still running.  Everything before pdl_wait() may only touch memory that no kernel of
+// the same step has written before it two or more launches back (parameters, BN statistics of
+// earlier kernels, its own shared memory / TMEM); pdl_wait() returns when the predecessor grid has
+// completed and its writes are visible.  pdl_trigger() (issued right after, so at most two grids ever
+// overlap) lets the successor start its own prologue.  Both are no-ops for ordinary launches.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() { pdl_wait(); pdl_trigger(); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -140,7 +150,7 @@ __device__ __forceinline__ bool last_cta_done(unsigned int* ticket, unsigned int
 // Optional in-kernel phase timestamps (build with -DDDPSTEP_TRACE): CTA 0 writes globaltimer values
 // into a small global buffer so latency chains inside a kernel can be read off directly.
 #ifdef DDPSTEP_TRACE
-__device__ unsigned long long g_trace[64];
+__device__ unsigned long long g_trace[256];  // kernel k owns slots 16k .. 16k+15 (0 = entry)
 __device__ __forceinline__ void trace_mark(int slot) {
   if (blockIdx.x == 0 && blockIdx.y == 0) {
     unsigned long long t;

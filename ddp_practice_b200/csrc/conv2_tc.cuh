@@ -142,6 +142,7 @@ struct Conv2TcArgs {
 
 template <typename T, int MODE>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
+  if (threadIdx.x == 0) TRACE((MODE == 0 ? 3 : 10) * 16 + 0);
   constexpr int PLANES = MODE == 0 ? 2 : 4;   // input channel groups of 8
   constexpr int N = MODE == 0 ? 32 : 16;      // output channels
   constexpr int KSTEPS = PLANES / 2;          // MMAs (K = 16) per tap
@@ -154,7 +155,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
   uint64_t *full = bars, *empty = bars + 2, *tfull = bars + 4, *tempty = bars + 6, *wbar = bars + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (MODE == 0 && tid == 0) TRACE(0);
 
   // ---- one-time setup: barriers, TMEM, and the 25 filter taps (ready-made K-major B tiles kept
   // up to date by the SGD kernel) fetched with one TMA copy
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  if (MODE == 0 && tid == 0) TRACE(1);
+  pdl_sync();  // predecessor wrote the input planes; barriers, TMEM and the filter tiles did not need it
   const int n_img = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // images of this CTA
   const unsigned char* gin = reinterpret_cast<const unsigned char*>(a.in);
 
@@ -207,13 +207,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       const uint32_t idesc = umma_idesc<T>(N);
       const uint32_t w_addr = smem_u32(w_s);
       mbar_wait(wbar, 0);
-      if (MODE == 0) TRACE(2);
       for (int i = 0; i < n_img; ++i) {
         const int s = i & 1;
         const uint32_t ph = (i >> 1) & 1;
         mbar_wait(&tempty[s], ph ^ 1);
         mbar_wait(&full[s], ph);
-        if (MODE == 0) TRACE(3);
         tc_fence_after();
         // descriptors differ from a per-image base only by compile-time constants: the whole tap loop is
         // unrolled so each MMA costs one 64-bit add per operand (a div/mod per tap made the single issuing
@@ -235,7 +233,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
             }
           }
         }
-        if (MODE == 0) TRACE(4);
         umma_commit(&empty[s]);   // smem stage may be refilled
         umma_commit(&tfull[s]);   // accumulators ready
       }
@@ -255,7 +252,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       const int s = i & 1;
       const int n = blockIdx.x + i * gridDim.x;
       mbar_wait(&tfull[s], (i >> 1) & 1);
-      if (MODE == 0 && tid == 64) TRACE(5);
       tc_fence_after();
 #pragma unroll 1
       for (int tile = 0; tile < 2; ++tile) {
@@ -279,7 +275,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       }
       tc_fence_before();
       mbar_arrive(&tempty[s]);
-      if (MODE == 0 && tid == 64) TRACE(6);
     }
     if (MODE == 0 && a.part != nullptr) {
       // deterministic CTA reduction of the per-thread statistics: butterfly inside the warp, then
@@ -300,7 +295,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       a.part[((size_t)blockIdx.x * 32 + c) * 2 + stat] = acc;
     }
   }
-  if (MODE == 0 && tid == 0) TRACE(7);
   if (warp == 0) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
@@ -309,7 +303,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
     if (!a.defer && last_cta_done(&a.ds->ticket[1], gridDim.x))
       finalize_fwd_stats<32>(a.part, gridDim.x, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
   }
-  if (MODE == 0 && tid == 0) TRACE(8);
 }
 
 
@@ -348,6 +341,7 @@ template <typename T> __device__ __forceinline__ uint32_t umma_idesc_mn(int n) {
 
 template <typename T>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcArgs a) {
+  if (threadIdx.x == 0) TRACE(8 * 16 + 0);
   extern __shared__ __align__(128) unsigned char wg_smem[];
   unsigned char* dy_s = wg_smem;                         // [2][4 planes]
   unsigned char* p_s = wg_smem + 2 * WG_DY_STAGE;        // [2][2 planes] + slack

@@ -128,12 +128,14 @@ constexpr int C1_GROUPS = 4;    // gridDim.y
 
 template <typename T>
 __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
+  if (threadIdx.x == 0) TRACE(1 * 16 + 0);
   __shared__ __align__(16) float xs[32 * C1_XS];
   __shared__ __align__(16) float ws[25 * 4];
   __shared__ float bs[4];
   __shared__ float red[4][8];
   const int tid = threadIdx.x, cg = blockIdx.y;
   T* __restrict__ y1 = reinterpret_cast<T*>(a.y1);
+  pdl_sync();  // first kernel of the step: nothing to wait for, lets the BN kernel start its prologue
 
   for (int i = tid; i < 32 * C1_XS; i += C1_THREADS) xs[i] = 0.f;
   if (tid < 100) {  // ws[k][j] <- rnd(W1[cg*4+j][k])
@@ -271,12 +273,15 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
     if (c < C) {
       double sm = 0.0, sq = 0.0;
       for (int l = 0; l < lanes; ++l) { sm += fin[l * COLS + 2 * c]; sq += fin[l * COLS + 2 * c + 1]; }
-      const double mean = sm / (double)local_count;
-      double var = sq / (double)local_count - mean * mean;
+      // sums are combined in double; the few divisions / the square root run in fp32 (an fp64 divide and
+      // sqrt chain costs ~1 us of pure latency here, and fp32 is what batch_norm_stats itself uses)
+      const double inv_n = (double)(1.0f / local_count);
+      const double mean = sm * inv_n;
+      double var = sq * inv_n - mean * mean;
       if (var < 0.0) var = 0.0;
       lmean = (float)mean;
-      linvstd = (float)(1.0 / sqrt(var + (double)a.eps));
-      lvar_unb = (float)(var * ((double)local_count / ((double)local_count - 1.0)));
+      linvstd = 1.0f / sqrtf((float)var + a.eps);
+      lvar_unb = (float)var * (local_count / (local_count - 1.0f));
       if (xchg && blockIdx.x == 0) {  // the all_gather of _functions.py:74, pushed by CTA 0
         for (int q = 0; q < a.comm.world; ++q) {
           float* slot = a.comm.peer[q]->slot_bn_fwd[a.layer][a.comm.rank];
@@ -345,6 +350,7 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
 
 template <typename T, int C, int H>
 __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
+  if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 0);
   constexpr int HP = H / 2;
   constexpr int OFF_G = (C == 16) ? OFF_G1 : OFF_G2, OFF_BE = (C == 16) ? OFF_BE1 : OFF_BE2;
   constexpr int RM = (C == 16) ? BNB_RM1 : BNB_RM2, RV = (C == 16) ? BNB_RV1 : BNB_RV2;
@@ -353,7 +359,9 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
     s_g[threadIdx.x] = a.params[OFF_G + threadIdx.x];
     s_b[threadIdx.x] = a.params[OFF_BE + threadIdx.x];
   }
+  pdl_sync();  // predecessor: the conv kernel that produced y and the partial statistics
   bn_forward_stats<C>(a, s_mean, s_invstd, RM, RV, (float)a.B * (float)(H * H));
+  if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 1);
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   T* __restrict__ p = reinterpret_cast<T*>(a.p);
   const size_t total = (size_t)a.B * C * HP * HP;
@@ -377,6 +385,7 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
       stf<T>(reinterpret_cast<T*>(a.p_planes) + (((size_t)(n * 2 + (c >> 3)) * 320 + (ph + 3) * 16 + pw) * 8 + (c & 7)), m);
     }
   }
+  if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 15);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -513,6 +522,7 @@ struct FcArgs {
 
 template <typename T>
 __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
+  if (threadIdx.x == 0) TRACE(5 * 16 + 0);
   __shared__ float red[7][10];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const T* __restrict__ p2 = reinterpret_cast<const T*>(a.p2);
@@ -525,6 +535,7 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
   float b[10];
 #pragma unroll
   for (int j = 0; j < 10; ++j) b[j] = rnd<T>(a.params[OFF_BFC + j]);
+  pdl_sync();  // predecessor: BN2 + ReLU + pool (p2); the weights above do not depend on it
   // incoming gradient of the loss: `scale` cast to the loss dtype (65536 -> inf in fp16)
   const float gl = a.use_scaler ? rnd<T>(a.ds->scale) : 1.0f;
   const float g = rnd<T>(-(gl / (float)a.B));

@@ -83,8 +83,10 @@ __global__ void __launch_bounds__(256) k_refresh_w2_tiles(const float* __restric
 
 template <typename T>
 __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS) k_step(StepArgs a) {
+  if (threadIdx.x == 0) TRACE(13 * 16 + 0);
   cg::cluster_group cluster = cg::this_cluster();
   __shared__ int s_nonfinite;
+  __shared__ int s_flags[STEP_CTAS];
   const int tid = threadIdx.x, cta = blockIdx.x;
   const int e = (cta * STEP_THREADS + tid) * 4;
   const bool valid = e < N_PARAM;  // last float4 (29032..29035) is half padding
@@ -97,6 +99,25 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   if (valid) {
     if (e + 4 <= N_PARAM) p4 = *reinterpret_cast<const float4*>(a.params + e);
     else { p4.x = a.params[e]; p4.y = a.params[e + 1]; }
+  }
+  pdl_sync();  // predecessor: conv1 weight gradient (the side branches are joined by full dependencies)
+  // CTA 0 owns the conv1 region (elements 0..415), whose gradient arrives as one partial row per
+  // conv1-wgrad CTA: all 1024 threads sum it together (9 row lanes per float4, one round trip to
+  // L2 instead of rows/8), fixed order.  Warp 0 also fetches the per-image losses now.
+  __shared__ float4 s_c1[9][104];
+  float nll_pref = 0.f;
+  if (cta == 0) {
+    const int e4 = tid % 104, rl = tid / 104;
+    if (rl < 9) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+      for (int r = rl; r < a.rows_conv1; r += 9) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(a.gpart + (size_t)r * N_PAD + 4 * e4));
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      s_c1[rl][e4] = acc;
+    }
+    if (tid < 32) for (int i = tid; i < a.B; i += 32) nll_pref += a.nll[i];
   }
   __syncthreads();
 
@@ -114,6 +135,14 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     if (round_t) {
       const float* p = a.gpart + e;
       if (a.gred != nullptr && e >= OFF_W2 && e < OFF_B2) { p = a.gred + e; rows = 1; }
+      if (e < OFF_G1) {  // conv1 region: lanes summed above, combine in fixed order
+        rows = 0;
+#pragma unroll
+        for (int l = 0; l < 9; ++l) {
+          const float4 v = s_c1[l][e >> 2];
+          g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        }
+      }
 #pragma unroll 8
       for (int r = 0; r < rows; ++r) {
         const float4 v = __ldcg(reinterpret_cast<const float4*>(p + (size_t)r * N_PAD));
@@ -168,15 +197,18 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     const bool bad = !(isfinite(u.x) && isfinite(u.y) && isfinite(u.z) && isfinite(u.w));
     if (valid && bad) atomicOr(&s_nonfinite, 1);
   }
-  // ---- 4. cluster-wide found_inf through distributed shared memory
+  // ---- 4. cluster-wide found_inf through distributed shared memory: every CTA writes its flag into
+  // slot [its rank] of ALL eight CTAs (the cluster is co-scheduled, so remote shared memory exists
+  // from the start), ONE cluster barrier, then everybody reads its own eight slots
+  __syncthreads();
+  if (tid < STEP_CTAS) *cluster.map_shared_rank(&s_flags[cta], tid) = s_nonfinite;
   cluster.sync();
   int found = 0;
 #pragma unroll
-  for (int r = 0; r < STEP_CTAS; ++r) found |= *cluster.map_shared_rank(&s_nonfinite, r);
-  cluster.sync();  // nobody may exit (and release its smem) before every CTA has read it
+  for (int r = 0; r < STEP_CTAS; ++r) found |= s_flags[r];
 
   // the gradient taps are stored only now: a release at cluster scope waits for every global
-  // store issued before it, so none may be in flight while the two barriers above run
+  // store issued before it, so none may be in flight while the barrier above runs
   if (valid) {
     if (e + 4 <= N_PARAM) {
       *reinterpret_cast<float4*>(a.grads_scaled + e) = tot;
@@ -202,9 +234,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
 
   // ---- 6. scalar state: loss, scale, tracker, epoch
   if (cta == 0 && tid < 32) {
-    float s = 0.f;
-    for (int i = tid; i < a.B; i += 32) s += a.nll[i];
-    s = warp_sum(s);
+    float s = warp_sum(nll_pref);
     if (tid == 0) {
       a.ds->loss = rnd<T>(s / (float)a.B);
       a.ds->found_inf = found ? 1.0f : 0.0f;
@@ -226,6 +256,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
       a.ds->epoch = epoch + 1ull;
     }
   }
+  if (threadIdx.x == 0) TRACE(13 * 16 + 15);
 }
 
 // dist.reduce(size, 0, SUM); dist.reduce(correct, 0, SUM)  (ddp_main.py:108-109): every
