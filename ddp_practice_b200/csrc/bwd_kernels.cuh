@@ -141,18 +141,13 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
       a.gdirect[OFF_G + tid] = f1 * a.st->invstd[tid];  // d(gamma), local: DDP averages it
       a.gdirect[OFF_BE + tid] = f0;                      // d(beta)
       if (xchg) {
+        const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
         for (int q = 0; q < a.comm.world; ++q) {
-          float* slot = a.comm.peer[q]->slot_bn_bwd[a.layer][a.comm.rank];
-          slot[tid] = f0;
-          slot[C + tid] = f1;
+          llword* slot = a.comm.peer[q]->ll_bn_bwd[a.layer][a.comm.rank];
+          ll_store(&slot[tid], f0, tag);
+          ll_store(&slot[C + tid], f1, tag);
         }
       }
-    }
-    if (xchg) {
-      __threadfence_system();
-      __syncthreads();
-      if (tid < a.comm.world)
-        st_release_sys(&a.comm.peer[tid]->flag_bn[2 + (1 - a.layer)][a.comm.rank], a.ds->epoch + 1ull);
     }
   }
 }
@@ -189,35 +184,26 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
       if (c < C) {
         a.gdirect[OFF_G + c] = s_loc[C + c] * inv_c;  // d(gamma), local: DDP averages it
         a.gdirect[OFF_BE + c] = s_loc[c];                        // d(beta)
-        if (xchg) {
+        if (xchg) {  // the all_reduce of _functions.py:159 as pushed self-validating words
+          const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
           for (int q = 0; q < a.comm.world; ++q) {
-            float* slot = a.comm.peer[q]->slot_bn_bwd[a.layer][a.comm.rank];
-            slot[c] = s_loc[c];
-            slot[C + c] = s_loc[C + c];
+            llword* slot = a.comm.peer[q]->ll_bn_bwd[a.layer][a.comm.rank];
+            ll_store(&slot[c], s_loc[c], tag);
+            ll_store(&slot[C + c], s_loc[C + c], tag);
           }
         }
       }
-      if (xchg) {
-        __threadfence_system();
-        __syncthreads();
-        if (c < a.comm.world)
-          st_release_sys(&a.comm.peer[c]->flag_bn[2 + (1 - a.layer)][a.comm.rank], a.ds->epoch + 1ull);
-      }
     }
-  }
-  if (xchg) {
-    if (c < a.comm.world)
-      wait_flag(&a.comm.self->flag_bn[2 + (1 - a.layer)][c], a.ds->epoch + 1ull, &a.ds->error);
-    __syncthreads();
   }
   if (c < C) {
     float s0, s1;
     if (xchg) {
       s0 = 0.f; s1 = 0.f;
+      const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
       for (int r = 0; r < a.comm.world; ++r) {
-        const float* slot = a.comm.self->slot_bn_bwd[a.layer][r];
-        s0 += __ldcg(&slot[c]);
-        s1 += __ldcg(&slot[C + c]);
+        const llword* slot = a.comm.self->ll_bn_bwd[a.layer][r];
+        s0 += ll_wait(&slot[c], tag, &a.ds->error);
+        s1 += ll_wait(&slot[C + c], tag, &a.ds->error);
       }
     } else if (a.defer) {
       s0 = s_loc[c];

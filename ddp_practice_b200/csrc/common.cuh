@@ -46,21 +46,22 @@ template <typename T> __device__ __forceinline__ float conv_out(float acc, float
 }
 
 // ---- cross-GPU symmetric region (identical layout on every rank) -----------------------
-// Exchanges are PUSH: the producer stores into every consumer's region and then raises a
-// flag there; consumers spin on their own memory only.  Flags carry a monotonically
-// increasing epoch (never reset), so a stale flag can never satisfy a later wait.
+// Exchanges are PUSH and fence-free: every value travels as ONE naturally aligned 8-byte word
+// {fp32 payload, 32-bit epoch tag} stored straight into the consumer's memory over NVLink (an
+// aligned 8-byte store is single-copy atomic), and the consumer polls its OWN memory until the tag
+// of the word it needs equals the epoch it is in -- the data is its own flag (the "LL" idea).  No
+// __threadfence_system, no separate flag store, no ordering between words: one NVLink store latency
+// per exchange.  Tags are epoch + 1 (never 0, never reused), so stale words can never match.
+typedef unsigned long long llword;
 struct alignas(128) SymRegion {
-  // flags[x][r]: rank r finished pushing exchange x for epoch == value
-  unsigned long long flag_bn[4][MAX_WORLD];                // 0 bn1 fwd, 1 bn2 fwd, 2 bn2 bwd, 3 bn1 bwd
-  unsigned long long flag_grad[MAX_WORLD][STEP_CTAS];      // per sender rank, per chunk (CTA)
+  alignas(128) llword ll_bn_fwd[2][MAX_WORLD][72];   // [layer][sender]: mean[C] invstd[C] count
+  alignas(128) llword ll_bn_bwd[2][MAX_WORLD][64];   // [layer][sender]: sum_dy[C] sum_dy_xmu[C]
+  alignas(128) llword ll_bnbuf[N_BNBUF + 4];         // rank 0's running buffers + 2 x nbt (lo, hi) (plain-BN DDP)
+  alignas(128) llword ll_inbox[2][MAX_WORLD][N_PAD]; // [step parity][sender][bucket element]
+  // test() counters: flag + slot protocol (off the training path)
   unsigned long long flag_counts[MAX_WORLD];
-  unsigned long long flag_counts_ack;                      // rank 0 consumed this rank's counters
-  alignas(128) float slot_bn_fwd[2][MAX_WORLD][68];                     // mean[C] invstd[C] count   (C <= 32)
-  alignas(128) float slot_bn_bwd[2][MAX_WORLD][64];                     // sum_dy[C] sum_dy_xmu[C]
+  unsigned long long flag_counts_ack;                // rank 0 consumed this rank's counters
   alignas(128) float slot_counts[MAX_WORLD][2];
-  alignas(128) float slot_bnbuf[N_BNBUF];                               // rank 0's running buffers (plain-BN DDP)
-  alignas(16) long long slot_nbt[2];
-  alignas(128) float inbox[2][MAX_WORLD][N_PAD];                        // [step parity][sender rank][bucket]
 };
 
 struct CommDev {
@@ -103,6 +104,25 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ llword ll_pack(float v, unsigned int tag) {
+  return ((llword)tag << 32) | (llword)__float_as_uint(v);
+}
+__device__ __forceinline__ void ll_store(llword* p, float v, unsigned int tag) {
+  asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(ll_pack(v, tag)) : "memory");
+}
+// Poll a word of this rank's own region until its tag matches; ~4 s timeout raises the error word.
+__device__ __forceinline__ float ll_wait(const llword* p, unsigned int tag, int* err) {
+  llword w;
+  long long t0 = 0;
+  for (int spin = 0;; ++spin) {
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    if ((unsigned int)(w >> 32) == tag) break;
+    if (spin == 64) t0 = clock64();
+    if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(err, 1); break; }
+  }
+  return __uint_as_float((unsigned int)w);
+}
+
 // Spin until *flag >= want; gives up after ~4 s and raises the error word so a dead peer
 // cannot hang the GPU forever.
 __device__ __forceinline__ void wait_flag(const unsigned long long* flag, unsigned long long want, int* err) {

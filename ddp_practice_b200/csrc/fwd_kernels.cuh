@@ -88,18 +88,14 @@ __device__ void finalize_fwd_stats(const float* part, int rows, float count, flo
     st->linvstd[c] = invstd;
     st->lvar_unbiased[c] = (float)(var * ((double)count / ((double)count - 1.0)));
     if (xchg) {
+      const unsigned int tag = (unsigned int)ds->epoch + 1u;
       for (int q = 0; q < comm.world; ++q) {
-        float* slot = comm.peer[q]->slot_bn_fwd[layer][comm.rank];
-        slot[c] = (float)mean;
-        slot[C + c] = invstd;
-        if (c == 0) slot[2 * C] = count;
+        llword* slot = comm.peer[q]->ll_bn_fwd[layer][comm.rank];
+        ll_store(&slot[c], (float)mean, tag);
+        ll_store(&slot[C + c], invstd, tag);
+        if (c == 0) ll_store(&slot[2 * C], count, tag);
       }
     }
-  }
-  if (xchg) {
-    __threadfence_system();
-    __syncthreads();
-    if (c < comm.world) st_release_sys(&comm.peer[c]->flag_bn[layer][comm.rank], ds->epoch + 1ull);
   }
 }
 
@@ -282,28 +278,20 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
       lmean = (float)mean;
       linvstd = 1.0f / sqrtf((float)var + a.eps);
       lvar_unb = (float)var * (local_count / (local_count - 1.0f));
-      if (xchg && blockIdx.x == 0) {  // the all_gather of _functions.py:74, pushed by CTA 0
+      if (xchg && blockIdx.x == 0) {  // the all_gather of _functions.py:74: CTA 0 pushes self-validating words
+        const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
         for (int q = 0; q < a.comm.world; ++q) {
-          float* slot = a.comm.peer[q]->slot_bn_fwd[a.layer][a.comm.rank];
-          slot[c] = lmean;
-          slot[C + c] = linvstd;
-          if (c == 0) slot[2 * C] = local_count;
+          llword* slot = a.comm.peer[q]->ll_bn_fwd[a.layer][a.comm.rank];
+          ll_store(&slot[c], lmean, tag);
+          ll_store(&slot[C + c], linvstd, tag);
+          if (c == 0) ll_store(&slot[2 * C], local_count, tag);
         }
       }
-    }
-    if (xchg && blockIdx.x == 0) {
-      __threadfence_system();
-      __syncthreads();
-      if (c < a.comm.world) st_release_sys(&a.comm.peer[c]->flag_bn[a.layer][a.comm.rank], a.ds->epoch + 1ull);
     }
   } else if (!a.eval && c < C) {
     lmean = a.st->lmean[c];
     linvstd = a.st->linvstd[c];
     lvar_unb = a.st->lvar_unbiased[c];
-  }
-  if (xchg) {
-    if (c < a.comm.world) wait_flag(&a.comm.self->flag_bn[a.layer][c], a.ds->epoch + 1ull, &a.ds->error);
-    __syncthreads();
   }
   if (c < C) {
     float mean, invstd, var_unb, n_total = local_count;
@@ -313,9 +301,11 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
       var_unb = 0.f;
     } else if (xchg) {
       float m = 0.f, m2 = 0.f, n = 0.f;
+      const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
       for (int r = 0; r < a.comm.world; ++r) {
-        const float* slot = a.comm.self->slot_bn_fwd[a.layer][r];
-        const float mu_r = __ldcg(&slot[c]), is_r = __ldcg(&slot[C + c]), n_r = __ldcg(&slot[2 * C]);
+        const llword* slot = a.comm.self->ll_bn_fwd[a.layer][r];
+        const float mu_r = ll_wait(&slot[c], tag, &a.ds->error), is_r = ll_wait(&slot[C + c], tag, &a.ds->error),
+                    n_r = ll_wait(&slot[2 * C], tag, &a.ds->error);
         const float v = (1.0f / (is_r * is_r) - a.eps) * n_r;
         const float f = 1.0f / (n + n_r);
         const float d = m - mu_r;

@@ -2,8 +2,9 @@
 //   * finish the weight-gradient partial sums, round to the autocast dtype (autocast keeps
 //     conv/linear weight gradients in that dtype: autocast_mode.h:824,840)
 //   * Reducer: bucket = grad * (1/W), all-reduce SUM        reducer.hpp:276, ddp_main.py:121
-//       -> one-shot push over NVLink peer memory into every rank's inbox, per-chunk flags,
-//          summed in fixed rank order so every replica gets identical bits
+//       -> one-shot push over NVLink peer memory into every rank's inbox as self-validating
+//          {value, epoch} words (no fence, no flags), summed in fixed rank order so every replica
+//          gets identical bits
 //   * GradScaler.unscale_: grad *= float(1/double(scale)), found_inf    grad_scaler.py:351-356
 //   * GradScaler.step: SGD p += (-lr) * g unless found_inf             grad_scaler.py:371, sgd.py:473
 //   * GradScaler.update: `_amp_update_scale_`                           grad_scaler.py:549-556
@@ -161,31 +162,41 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   float4 tot = h;
   if (W > 1) {
     const int par = (int)(epoch & 1ull);
-    if (valid) {
+    const unsigned int tag = (unsigned int)epoch + 1u;
+    if (valid) {  // every element travels with its own tag: no fence, no flag, no block-level synchronisation
+      const ulonglong2 w01 = make_ulonglong2(ll_pack(h.x, tag), ll_pack(h.y, tag));
+      const ulonglong2 w23 = make_ulonglong2(ll_pack(h.z, tag), ll_pack(h.w, tag));
       for (int q = 0; q < W; ++q)
-        if (q != rank) *reinterpret_cast<float4*>(&a.comm.peer[q]->inbox[par][rank][e]) = h;
+        if (q != rank) {
+          ulonglong2* dst = reinterpret_cast<ulonglong2*>(&a.comm.peer[q]->ll_inbox[par][rank][e]);
+          asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(w01.x), "l"(w01.y) : "memory");
+          asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 1), "l"(w23.x), "l"(w23.y) : "memory");
+        }
     }
-    if (!a.sync && rank == 0 && cta == 0) {  // plain-BN DDP: rank 0's buffers win
-      for (int q = 1; q < W; ++q) {
-        if (tid < N_BNBUF) a.comm.peer[q]->slot_bnbuf[tid] = a.bnbuf[tid];
-        if (tid < 2) a.comm.peer[q]->slot_nbt[tid] = a.nbt[tid];
+    if (!a.sync && cta == 0) {  // plain-BN DDP: rank 0's buffers win (distributed.py:2243-2257)
+      if (rank == 0) {
+        for (int q = 1; q < W; ++q) {
+          if (tid < N_BNBUF) ll_store(&a.comm.peer[q]->ll_bnbuf[tid], a.bnbuf[tid], tag);
+          if (tid < 4) ll_store(&a.comm.peer[q]->ll_bnbuf[N_BNBUF + tid],
+                                __uint_as_float(reinterpret_cast<const unsigned int*>(a.nbt)[tid]), tag);
+        }
+      } else {
+        if (tid < N_BNBUF) a.bnbuf[tid] = ll_wait(&a.comm.self->ll_bnbuf[tid], tag, &a.ds->error);
+        if (tid < 4) reinterpret_cast<unsigned int*>(a.nbt)[tid] =
+            __float_as_uint(ll_wait(&a.comm.self->ll_bnbuf[N_BNBUF + tid], tag, &a.ds->error));
       }
     }
-    __threadfence_system();
-    __syncthreads();
-    if (tid < W && tid != rank) st_release_sys(&a.comm.peer[tid]->flag_grad[rank][cta], epoch + 1ull);
-    if (tid < W && tid != rank) wait_flag(&a.comm.self->flag_grad[tid][cta], epoch + 1ull, &a.ds->error);
-    __syncthreads();
     if (valid) {
       tot = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int q = 0; q < W; ++q) {
-        const float4 v = (q == rank) ? h : __ldcg(reinterpret_cast<const float4*>(&a.comm.self->inbox[par][q][e]));
+        float4 v = h;
+        if (q != rank) {
+          const llword* src = &a.comm.self->ll_inbox[par][q][e];
+          v.x = ll_wait(src, tag, &a.ds->error); v.y = ll_wait(src + 1, tag, &a.ds->error);
+          v.z = ll_wait(src + 2, tag, &a.ds->error); v.w = ll_wait(src + 3, tag, &a.ds->error);
+        }
         tot.x += v.x; tot.y += v.y; tot.z += v.z; tot.w += v.w;
       }
-    }
-    if (!a.sync && rank != 0 && cta == 0) {
-      if (tid < N_BNBUF) a.bnbuf[tid] = __ldcg(&a.comm.self->slot_bnbuf[tid]);
-      if (tid < 2) a.nbt[tid] = a.comm.self->slot_nbt[tid];
     }
   }
 
