@@ -200,10 +200,12 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
     if (xchg) {
       s0 = 0.f; s1 = 0.f;
       const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
-      for (int r = 0; r < a.comm.world; ++r) {
-        const llword* slot = a.comm.self->ll_bn_bwd[a.layer][r];
-        s0 += ll_wait(&slot[c], tag, &a.ds->error);
-        s1 += ll_wait(&slot[C + c], tag, &a.ds->error);
+      float got[MAX_WORLD * 2];
+      const int idx[2] = {c, C + c};
+      ll_gather<2>(&a.comm.self->ll_bn_bwd[a.layer][0][0], 64, idx, 0, a.comm.world, tag, got, &a.ds->error);
+#pragma unroll
+      for (int r = 0; r < MAX_WORLD; ++r) {  // fixed rank order
+        if (r < a.comm.world) { s0 += got[r * 2]; s1 += got[r * 2 + 1]; }
       }
     } else if (a.defer) {
       s0 = s_loc[c];

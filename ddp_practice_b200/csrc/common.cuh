@@ -123,6 +123,38 @@ __device__ __forceinline__ float ll_wait(const llword* p, unsigned int tag, int*
   return __uint_as_float((unsigned int)w);
 }
 
+__device__ __forceinline__ llword ll_ld(const llword* p) {
+  llword w;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+  return w;
+}
+// Gather NW words from each of `world` senders (sender r's word j at base + r*stride + idx[j]).  All
+// loads of one polling round are issued together, so a round costs ONE L2 round trip instead of
+// world x NW dependent ones; rounds repeat until every tag matches.  out[r*NW + j] = payload.
+template <int NW, int NR = MAX_WORLD>
+__device__ __forceinline__ void ll_gather(const llword* base, size_t stride, const int (&idx)[NW], int r0, int world,
+                                          unsigned int tag, float* out, int* err) {
+  long long t0 = 0;
+  for (int spin = 0;; ++spin) {
+    llword w[NR * NW];
+#pragma unroll
+    for (int r = 0; r < NR; ++r)
+#pragma unroll
+      for (int j = 0; j < NW; ++j)
+        w[r * NW + j] = (r0 + r) < world ? ll_ld(base + (size_t)(r0 + r) * stride + idx[j]) : ((llword)tag << 32);
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < NR * NW; ++i) ok = ok && ((unsigned int)(w[i] >> 32) == tag);
+    if (ok) {
+#pragma unroll
+      for (int i = 0; i < NR * NW; ++i) out[i] = __uint_as_float((unsigned int)w[i]);
+      return;
+    }
+    if (spin == 64) t0 = clock64();
+    if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(err, 1); return; }
+  }
+}
+
 // Spin until *flag >= want; gives up after ~4 s and raises the error word so a dead peer
 // cannot hang the GPU forever.
 __device__ __forceinline__ void wait_flag(const unsigned long long* flag, unsigned long long want, int* err) {

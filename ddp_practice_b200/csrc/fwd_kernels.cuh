@@ -302,10 +302,13 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
     } else if (xchg) {
       float m = 0.f, m2 = 0.f, n = 0.f;
       const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
-      for (int r = 0; r < a.comm.world; ++r) {
-        const llword* slot = a.comm.self->ll_bn_fwd[a.layer][r];
-        const float mu_r = ll_wait(&slot[c], tag, &a.ds->error), is_r = ll_wait(&slot[C + c], tag, &a.ds->error),
-                    n_r = ll_wait(&slot[2 * C], tag, &a.ds->error);
+      float got[MAX_WORLD * 3];
+      const int idx[3] = {c, C + c, 2 * C};
+      ll_gather<3>(&a.comm.self->ll_bn_fwd[a.layer][0][0], 72, idx, 0, a.comm.world, tag, got, &a.ds->error);
+#pragma unroll
+      for (int r = 0; r < MAX_WORLD; ++r) {
+        if (r >= a.comm.world) break;
+        const float mu_r = got[r * 3], is_r = got[r * 3 + 1], n_r = got[r * 3 + 2];
         const float v = (1.0f / (is_r * is_r) - a.eps) * n_r;
         const float f = 1.0f / (n + n_r);
         const float d = m - mu_r;

@@ -29,6 +29,8 @@ struct StepArgs {
   const float* gred;    // [N_PAD] conv2-weight partial rows already summed (k_reduce_rows), or null
   const float* gdirect; // [N_PAD]
   const float* nll;     // [B]
+  volatile float* host_mail;  // pinned host memory {loss, step counter as float bits}: lets the host API return the
+                        // loss by polling instead of a D2H copy + stream synchronisation; may be null
   float* bnbuf;
   long long* nbt;
   DevState* ds;
@@ -187,15 +189,20 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
       }
     }
     if (valid) {
+      // this rank's own contribution is stored locally too, so one gather covers all W senders
+      llword* mine = &a.comm.self->ll_inbox[par][rank][e];
+      ll_store(mine, h.x, tag); ll_store(mine + 1, h.y, tag); ll_store(mine + 2, h.z, tag); ll_store(mine + 3, h.w, tag);
+      const int idx[4] = {0, 1, 2, 3};
       tot = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int q = 0; q < W; ++q) {
-        float4 v = h;
-        if (q != rank) {
-          const llword* src = &a.comm.self->ll_inbox[par][q][e];
-          v.x = ll_wait(src, tag, &a.ds->error); v.y = ll_wait(src + 1, tag, &a.ds->error);
-          v.z = ll_wait(src + 2, tag, &a.ds->error); v.w = ll_wait(src + 3, tag, &a.ds->error);
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {  // two gathers of four senders keep the 1024-thread CTA within 64 registers
+        if (half * 4 < W) {
+          float got[16];
+          ll_gather<4, 4>(&a.comm.self->ll_inbox[par][0][e], N_PAD, idx, half * 4, W, tag, got, &a.ds->error);
+#pragma unroll
+          for (int q = 0; q < 4; ++q)  // fixed rank order
+            if (half * 4 + q < W) { tot.x += got[q * 4]; tot.y += got[q * 4 + 1]; tot.z += got[q * 4 + 2]; tot.w += got[q * 4 + 3]; }
         }
-        tot.x += v.x; tot.y += v.y; tot.z += v.z; tot.w += v.w;
       }
     }
   }
@@ -265,6 +272,11 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
         }
       }
       a.ds->epoch = epoch + 1ull;
+      if (a.host_mail != nullptr) {
+        a.host_mail[0] = rnd<T>(s / (float)a.B);
+        __threadfence_system();
+        reinterpret_cast<volatile unsigned int*>(a.host_mail)[1] = (unsigned int)epoch + 1u;
+      }
     }
   }
   if (threadIdx.x == 0) TRACE(13 * 16 + 15);

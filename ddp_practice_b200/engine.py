@@ -63,6 +63,8 @@ class Engine:
         p = _lib.Ptrs()
         self._check(self.lib.ddpstep_state_ptrs(self.ctx, C.byref(p)))
         self._ptrs = p
+        self._loss_out = C.c_float()
+        self._loss_ref = C.byref(self._loss_out)
         dev = f"cuda:{self.device}"
         view = lambda ptr, shape, ts: torch.as_tensor(_DevArray(ptr, shape, ts, self), device=dev)
         # zero-copy views of the library's state
@@ -141,11 +143,14 @@ class Engine:
 
     def train_step_host(self, x: torch.Tensor, y: torch.Tensor, want_loss: bool = True):
         """Same from (pinned) host tensors; returns the loss (synchronises) if asked."""
-        assert not x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
-        assert not y.is_cuda and y.dtype == torch.int64 and y.is_contiguous()
-        loss = C.c_float()
-        self._check(self.lib.ddpstep_train_step_host(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0],
-                                                     C.byref(loss) if want_loss else None, self._stream()))
+        if x.is_cuda or y.is_cuda or x.dtype != torch.float32 or y.dtype != torch.int64 or not (
+                x.is_contiguous() and y.is_contiguous()):
+            raise ValueError("train_step_host wants contiguous CPU tensors: fp32 images, int64 labels")
+        loss = self._loss_out
+        rc = self.lib.ddpstep_train_step_host(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0],
+                                              self._loss_ref if want_loss else None, self._stream())
+        if rc != 0:
+            self._check(rc)
         return loss.value if want_loss else None
 
     def eval_batch(self, x: torch.Tensor, y: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -34,7 +34,7 @@ int main() {
       {"all rows = 0", 0, 0, 0, 0, true, false},
   };
   for (auto& v : vs) {
-    StepArgs a{params, grads, gs, gpart, v.red ? gred : nullptr, gdirect, nll, bnbuf, nbt, ds, comm, 32,
+    StepArgs a{params, grads, gs, gpart, v.red ? gred : nullptr, gdirect, nll, nullptr, bnbuf, nbt, ds, comm, 32,
                v.r1, v.r2w, v.r2b, v.rfc, 1, 1, 1e-4f, 2.f, 0.5f, 2000};
     float us = time_graph([&](cudaStream_t s) { k_step<__half><<<STEP_CTAS, STEP_THREADS, 0, s>>>(a); }, 8, 500);
     printf("%-42s : %.2f us\n", v.name, us);
