@@ -49,7 +49,7 @@ struct ddpstep_ctx {
   void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
   void *p1h = nullptr, *dy2h = nullptr, *w2_tiles = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
-  bool use_tc = false, use_wgrad_tc = false, use_pdl = true;
+  bool use_tc = false, use_wgrad_tc = false, use_pdl = true, last_planes = false;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   float* x_stage = nullptr;
   int64_t* y_stage = nullptr;
@@ -368,7 +368,18 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 2. BN1 + ReLU + pool
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps,
                 defer1 ? c->part1 : nullptr, g1};
-  launch_k(k_bn_relu_pool<T, 16, 28>, dim3(clampi(cdiv(B * 16 * 196, 256), 1, 1184)), dim3(256), 0, s, b1, pdl); mark();
+  bool planes = false;
+  // large batches: write p1 / d(conv2 out) only as padded planes with 16-byte stores (nobody reads the NCHW copies);
+  // small batches keep the one-thread-per-element kernels, whose shorter per-thread chains give lower latency
+  if constexpr (!std::is_same<T, float>::value) planes = c->use_tc && c->use_wgrad_tc && B > 64;
+  c->last_planes = planes;
+  if (planes) {
+    if constexpr (!std::is_same<T, float>::value)
+      launch_k(k_bn1_relu_pool_planes<T>, dim3(clampi(cdiv(B * 2 * 196, 256), 1, 1184)), dim3(256), 0, s, b1, pdl);
+  } else {
+    launch_k(k_bn_relu_pool<T, 16, 28>, dim3(clampi(cdiv(B * 16 * 196, 256), 1, 1184)), dim3(256), 0, s, b1, pdl);
+  }
+  mark();
   // 3. conv2 + local BN2 statistics
   const int g2 = std::min(B, 148);
   Conv14Args a2{c->p1, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
@@ -401,8 +412,17 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);
   BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, 1, ns2, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
+  // the plane-writing apply kernel has 4 channel groups per batch split: use more splits to fill the GPU
+  const int ns2p = clampi(cdiv(B, 2), 1, 64);
+  BnBwdArgs r2p = r2;
+  r2p.per_split = cdiv(B, ns2p);
   launch_k(k_bn_bwd_reduce<T, 32, 14>, dim3(32, ns2), dim3(256), 0, s, r2, pdl); mark();
-  launch_k(k_bn2_bwd_apply<T>, dim3(32, ns2), dim3(256), 0, s, r2, pdl); mark();
+  if (planes) {
+    if constexpr (!std::is_same<T, float>::value) launch_k(k_bn2_bwd_apply_planes<T>, dim3(4, ns2p), dim3(256), 0, s, r2p, pdl);
+  } else {
+    launch_k(k_bn2_bwd_apply<T>, dim3(32, ns2), dim3(256), 0, s, r2, pdl);
+  }
+  mark();
   // 9. conv2 weight gradient partials, 10. conv2 data gradient
   const int gw = std::min(B, 37);
   Conv2WgradArgs w2{c->p1, c->dy2, c->gpart, B};
@@ -445,7 +465,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   launch_k(k_conv1_wgrad<T>, dim3(gc1, 4), dim3(C1W_THREADS), 0, s, cw, pdl); mark();
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->host_mail, c->bnbuf, c->nbt, c->ds, c->comm, B,
-              gc1, gw_rows, ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
+              gc1, gw_rows, planes ? ns2p : ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();
   return cudaGetLastError();
@@ -475,7 +495,15 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
   if (rec) rec->a_c1 = a1;
   k_conv1_fwd<T><<<dim3(std::min(B, 296), C1_GROUPS), C1_THREADS, 0, s>>>(a1); mark();
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, c->st, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 1, 0, cfg.bn_momentum, cfg.bn_eps, nullptr, 0};
-  k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1); mark();
+  bool planes = false;
+  if constexpr (!std::is_same<T, float>::value) planes = c->use_tc && B > 64;
+  c->last_planes = planes;
+  if (planes) {
+    if constexpr (!std::is_same<T, float>::value) k_bn1_relu_pool_planes<T><<<clampi(cdiv(B * 2 * 196, 256), 1, 1184), 256, 0, s>>>(b1);
+  } else {
+    k_bn_relu_pool<T, 16, 28><<<clampi(cdiv(B * 16 * 196, 256), 1, 1184), 256, 0, s>>>(b1);
+  }
+  mark();
   Conv14Args a2{c->p1, c->params, c->y2, nullptr, 0, c->st + 1, c->ds, c->comm, B, dbl, 0, cfg.bn_eps};
   bool tc = false;
   if constexpr (!std::is_same<T, float>::value) {
@@ -706,6 +734,23 @@ extern "C" int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* ho
   if (which < 0 || which > 6) return fail(ctx, DDPSTEP_E_ARG, "bad activation id %d", which);
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaDeviceSynchronize());
+  const bool planes = ctx->last_planes && (which == 1 || which == 5);
+  if (planes) {
+    // on the tensor-core path p1 and d(conv2 out) exist only in the padded-plane layout: convert to NCHW here
+    const int ch = which == 1 ? 16 : 32, npl = ch / 8;
+    std::vector<uint16_t> pl((size_t)B * npl * 320 * 8);
+    CK(cudaMemcpy(pl.data(), which == 1 ? ctx->p1h : ctx->dy2h, pl.size() * 2, cudaMemcpyDeviceToHost));
+    uint16_t* out = static_cast<uint16_t*>(host);
+    const size_t max_el = (size_t)bytes / 2;
+    for (size_t n = 0; n < B; ++n)
+      for (int c = 0; c < ch; ++c)
+        for (int h = 0; h < 14; ++h)
+          for (int w = 0; w < 14; ++w) {
+            const size_t o = ((n * ch + c) * 14 + h) * 14 + w;
+            if (o < max_el) out[o] = pl[((n * npl + (c >> 3)) * 320 + (h + 3) * 16 + w) * 8 + (c & 7)];
+          }
+    return 0;
+  }
   CK(cudaMemcpy(host, src[which], std::min((size_t)bytes, sz[which]), cudaMemcpyDeviceToHost));
   return 0;
 }

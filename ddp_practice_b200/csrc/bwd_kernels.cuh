@@ -274,6 +274,75 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
   if (threadIdx.x == 0) TRACE(9 * 16 + 15);
 }
 
+// Same, for the tensor-core path: d(conv2 out) is written ONLY in the padded-plane layout
+// (conv2_tc.cuh), thread = one pooling window x 8 channels -> four 16-byte stores.  grid (4 channel
+// groups, NS batch splits).
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn2_bwd_apply_planes(BnBwdArgs a) {
+  constexpr int C = 32, H = 14, HP = 7;
+  __shared__ float s_k1[C], s_k2[C];
+  __shared__ float s_c[8][4];  // this group's channels: mean, invstd, gamma, beta
+  __shared__ float red[8][8];
+  const int tid = threadIdx.x, g = blockIdx.x;
+  float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
+  if (tid < 8) {  // independent of the predecessor: issued before the wait inside bn_backward_sums
+    const int c = g * 8 + tid;
+    c0 = a.st->mean[c]; c1 = a.st->invstd[c]; c2 = a.params[OFF_G2 + c]; c3 = a.params[OFF_BE2 + c];
+  }
+  bn_backward_sums<C>(a, s_k1, s_k2);
+  if (tid < 8) { s_c[tid][0] = c0; s_c[tid][1] = c1; s_c[tid][2] = c2; s_c[tid][3] = c3; }
+  __syncthreads();
+  const int n0 = blockIdx.y * a.per_split, n1 = min(a.B, n0 + a.per_split);
+  const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
+  const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
+  T* __restrict__ pl = reinterpret_cast<T*>(a.dy_planes);
+  float bsum[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bsum[j] = 0.f;
+  const int total = max(0, n1 - n0) * HP * HP;
+  for (int e = tid; e < total; e += 256) {
+    const int n = n0 + e / (HP * HP), w = e % (HP * HP), ph = w / HP, pw = w % HP;
+    float o[4][8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      const size_t off = (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
+      float v[4];
+      load2<T>(y + off, v[0], v[1]);
+      load2<T>(y + off + H, v[2], v[3]);
+      const float mu = s_c[j][0], is = s_c[j][1], gm = s_c[j][2];
+      bool live;
+      const int arg = pool_winner<T>(v, mu, is, gm, s_c[j][3], live);
+      const float d = live ? ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]) : 0.f;
+      const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * gm;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float da = (live && i == arg) ? d : 0.f;
+        o[i][j] = rnd<T>((da - k1 - (v[i] - mu) * k2) * k3);
+        bsum[j] += o[i][j];
+      }
+    }
+    T* dst = pl + (((size_t)(n * 4 + g) * 320 + (2 * ph + 3) * 16 + 2 * pw) * 8);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      T* d2 = dst + ((i >> 1) * 16 + (i & 1)) * 8;
+      store4<T>(d2, o[i][0], o[i][1], o[i][2], o[i][3]);
+      store4<T>(d2 + 4, o[i][4], o[i][5], o[i][6], o[i][7]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float v = warp_sum(bsum[j]);
+    if ((tid & 31) == 0) red[tid >> 5][j] = v;
+  }
+  __syncthreads();
+  if (tid < 8) {
+    float v = 0.f;
+    for (int w = 0; w < 8; ++w) v += red[w][tid];
+    a.gpart[(size_t)blockIdx.y * N_PAD + OFF_B2 + g * 8 + tid] = v;
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // conv2 weight gradient: dW[co][ci][kh][kw] = sum_{n,h,w} dy2[n,co,h,w] * p1[n,ci,h+kh-2,w+kw-2]
 // grid (GX images-strided, 4 groups of 8 output channels), 160 threads = 16 ci x 5 kh x 2

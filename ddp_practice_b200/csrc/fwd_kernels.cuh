@@ -381,6 +381,46 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
   if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 15);
 }
 
+// Same for layer 1 when conv2 runs on the tensor cores: the pooled output is written ONLY in the
+// padded-plane layout conv2_tc.cuh consumes ([image][channel/8][20x16 pixels][8 channels]), one
+// thread per pixel and group of 8 channels, i.e. one 16-byte store per thread.
+template <typename T>
+__global__ void __launch_bounds__(256) k_bn1_relu_pool_planes(BnPoolArgs a) {
+  constexpr int C = 16, H = 28;
+  __shared__ float s_mean[C], s_invstd[C], s_g[C], s_b[C];
+  if (threadIdx.x < C) {
+    s_g[threadIdx.x] = a.params[OFF_G1 + threadIdx.x];
+    s_b[threadIdx.x] = a.params[OFF_BE1 + threadIdx.x];
+  }
+  pdl_sync();
+  bn_forward_stats<C>(a, s_mean, s_invstd, BNB_RM1, BNB_RV1, (float)a.B * (float)(H * H));
+  const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
+  T* __restrict__ pl = reinterpret_cast<T*>(a.p_planes);
+  const size_t total = (size_t)a.B * 2 * 196;
+  for (size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (size_t)gridDim.x * 256) {
+    const int pw = (int)(idx % 14), ph = (int)((idx / 14) % 14), g = (int)((idx / 196) & 1);
+    const size_t n = idx / 392;
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      const T* src = y + ((n * C + c) * H + 2 * ph) * H + 2 * pw;
+      float v0, v1, v2, v3;
+      load2<T>(src, v0, v1);
+      load2<T>(src + H, v2, v3);
+      const float mu = s_mean[c], is = s_invstd[c], gm = s_g[c], b = s_b[c];
+      v0 = rnd<T>((v0 - mu) * is * gm + b);
+      v1 = rnd<T>((v1 - mu) * is * gm + b);
+      v2 = rnd<T>((v2 - mu) * is * gm + b);
+      v3 = rnd<T>((v3 - mu) * is * gm + b);
+      o[j] = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
+    }
+    T* dst = pl + (((n * 2 + g) * 320 + (ph + 3) * 16 + pw) * 8);
+    store4<T>(dst, o[0], o[1], o[2], o[3]);
+    store4<T>(dst + 4, o[4], o[5], o[6], o[7]);
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // 5x5 pad-2 convolution on 14x14 planes, direct form.  MODE 0: conv2 forward (16->32, bias,
 // BN statistics).  MODE 2: conv2 data gradient (32->16): the same correlation with the kernel
