@@ -459,7 +459,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   const int ns1 = clampi(cdiv(B, 2), 1, 32);
   BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, 1, ns1, nullptr, nullptr, c->gpart};
   launch_k(k_bn_bwd_reduce<T, 16, 28>, dim3(16, ns1), dim3(256), 0, s, r1, pdl); mark();
-  const int gc1 = std::min(B, 148);
+  const int gc1 = std::min(B, 296);
   Conv1WgradArgs cw{r1, x};
   if (rec) rec->a_c1w = cw;
   launch_k(k_conv1_wgrad<T>, dim3(gc1, 4), dim3(C1W_THREADS), 0, s, cw, pdl); mark();

@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
   pdl_sync();  // predecessor produced dpool; the statistics above come from an earlier kernel
   float sdy = 0.f, sdyx = 0.f;
   const int total = max(0, n1 - n0) * HP * HP;
+#pragma unroll 4
   for (int e = tid; e < total; e += 256) {
     const int n = n0 + e / (HP * HP), w = e % (HP * HP), ph = w / HP, pw = w % HP;
     const T* src = y + (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;

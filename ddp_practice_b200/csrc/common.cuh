@@ -19,7 +19,7 @@ constexpr int BNB_RM1 = 0, BNB_RV1 = 16, BNB_RM2 = 32, BNB_RV2 = 64, N_BNBUF = 9
 constexpr int MAX_WORLD = 8;
 constexpr int STEP_CTAS = 8;        // one cluster
 constexpr int STEP_THREADS = 1024;  // 8 * 1024 * 4 = 32768 >= N_PAD
-constexpr int MAX_PART_ROWS = 160;  // rows of the weight-gradient partial buffer
+constexpr int MAX_PART_ROWS = 320;  // rows of the weight-gradient partial buffer
 
 // ---- storage dtype helpers -------------------------------------------------------------
 template <typename T> struct Cvt;

@@ -358,6 +358,7 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   T* __restrict__ p = reinterpret_cast<T*>(a.p);
   const size_t total = (size_t)a.B * C * HP * HP;
+#pragma unroll 4
   for (size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (size_t)gridDim.x * 256) {
     const int pw = (int)(idx % HP), ph = (int)((idx / HP) % HP);
     const size_t plane = idx / (HP * HP);
