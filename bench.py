@@ -262,7 +262,11 @@ def main():
     else:
         ach = (ab * es + xb) * B / sec / 1e9
         roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak}
-    roof.update({"traffic": None, "peak_source": peak_src, "avg_kernel_us": prof[dom] * 1e3,
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tpath) and B == 32 and args.dtype == "fp16":  # the capture was taken on this configuration
+        traffic = json.load(open(tpath)).get(dom)
+    roof.update({"traffic": traffic, "peak_source": peak_src, "avg_kernel_us": prof[dom] * 1e3,
                  "how": f"CUDA events between the kernel nodes of the step graph, mean of {n_prof} steps",
                  "kernel_us": {k: round(v * 1e3, 2) for k, v in prof.items()},
                  "step_hbm_frac": (STEP_BYTES_PER_IMG_AMP * (es / 2) * B + STEP_PARAM_BYTES) / (ms_total / K * 1e-3) / 1e9 / hbm_peak,
