@@ -361,6 +361,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
   // 1. conv1 + local BN1 statistics
   const int g1 = std::min(B, 296);
   // small grids: the BN kernels reduce the conv kernels' partial sums themselves (no last-CTA tail)
+  const int tsplit = B <= 64 ? 2 : 1;  // tcgen05 conv2: one M-tile per CTA at small batch
   const int defer1 = g1 <= 64, defer2 = std::min(B, 148) <= 64;
   Conv1Args a1{x, c->params, c->y1, c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
@@ -389,14 +390,14 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
       tc = true;
       if (fork) cudaStreamWaitEvent(s, c->ev_j0, 0);
       Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
-      launch_k(k_conv2_tc<T, 0>, dim3(g2), dim3(TC_THREADS), tc_smem_bytes(2), s, t2, pdl);
+      launch_k(k_conv2_tc<T, 0>, dim3(g2, tsplit), dim3(TC_THREADS), tc_smem_bytes(2), s, t2, pdl);
     }
   }
   if (!tc) k_conv14<T, 16, 32, 0><<<dim3(g2, 4), 128, (16 * 18 * C14_RS + 8 * 16 * 25) * 4, s>>>(a2);
   mark();
   // 4. BN2 + ReLU + pool
   BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps,
-                defer2 ? c->part2 : nullptr, g2};
+                defer2 ? c->part2 : nullptr, tc ? g2 * tsplit : g2};
   launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark();
   // 5. Linear + CE + dlogits + d(pool2 out)
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, c->dlogits, c->dflat, c->nll, c->counts,
@@ -434,7 +435,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
     if (c->use_tc) {
       tc = true;
       Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
-      launch_k(k_conv2_tc<T, 2>, dim3(std::min(B, 148)), dim3(TC_THREADS), tc_smem_bytes(4), s, t2, pdl);
+      launch_k(k_conv2_tc<T, 2>, dim3(std::min(B, 148), tsplit), dim3(TC_THREADS), tc_smem_bytes(4), s, t2, pdl);
     }
   }
   if (!tc) k_conv14<T, 32, 16, 2><<<dim3(std::min(B, 296), 2), 128, (32 * 18 * C14_RS + 8 * 32 * 25) * 4, s>>>(d2);

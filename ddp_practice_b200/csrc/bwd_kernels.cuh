@@ -481,7 +481,7 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
     if (tid < 140) {
 #pragma unroll
       for (int hh = 0; hh < 4; ++hh) {
-        const int h = rs * 4 + hh;
+        const int h = hh * 7 + rs;  // lanes of a warp read consecutive rows: bank-conflict free 16-byte loads
         const float* drow = dy_s + (col * 28 + h) * 28;
         const float* xrow = xs + (h + kh) * C1_XS;
 #pragma unroll

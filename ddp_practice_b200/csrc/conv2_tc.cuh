@@ -188,6 +188,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
   const uint32_t tmem_base = *tmem_slot;
   pdl_sync();  // predecessor wrote the input planes; barriers, TMEM and the filter tiles did not need it
   const int n_img = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // images of this CTA
+  // gridDim.y == 2 (small batches): each CTA computes ONE of the two M-tiles of its images, so twice as many SMs
+  // share the MMA and epilogue work; gridDim.y == 1: both tiles, every image is fetched once
+  const int tile_lo = gridDim.y == 2 ? (int)blockIdx.y : 0, tile_hi = gridDim.y == 2 ? (int)blockIdx.y + 1 : 2;
   const unsigned char* gin = reinterpret_cast<const unsigned char*>(a.in);
 
   if (warp == 0) {
@@ -220,6 +223,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
         const uint64_t bd0 = umma_desc(w_addr, N * 16, 128);
 #pragma unroll
         for (int tile = 0; tile < 2; ++tile) {
+          if (tile < tile_lo || tile >= tile_hi) continue;
           const uint32_t d = tmem_base + (uint32_t)((s * 2 + tile) * N);
 #pragma unroll
           for (int tap = 0; tap < 25; ++tap) {
@@ -254,7 +258,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
       mbar_wait(&tfull[s], (i >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int tile = 0; tile < 2; ++tile) {
+      for (int tile = tile_lo; tile < tile_hi; ++tile) {
         float v[N];
         tmem_ld_row<N>(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((s * 2 + tile) * N), v);
         const int m = tile * 128 + et, h = m >> 4, w = m & 15;
@@ -292,7 +296,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
     if (tid < 64) {
       const float acc = ((red[tid] + red[64 + tid]) + red[128 + tid]) + red[192 + tid];
       const int c = tid & 31, stat = tid >> 5;
-      a.part[((size_t)blockIdx.x * 32 + c) * 2 + stat] = acc;
+      a.part[((size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 32 + c) * 2 + stat] = acc;
     }
   }
   if (warp == 0) {
@@ -300,8 +304,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
   }
   if (MODE == 0 && a.part != nullptr) {
-    if (!a.defer && last_cta_done(&a.ds->ticket[1], gridDim.x))
-      finalize_fwd_stats<32>(a.part, gridDim.x, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
+    if (!a.defer && last_cta_done(&a.ds->ticket[1], gridDim.x * gridDim.y))
+      finalize_fwd_stats<32>(a.part, gridDim.x * gridDim.y, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
   }
 }
 
