@@ -94,3 +94,42 @@ def test_shim_rejects_misuse():
         GradScaler().step(opt)
     with pytest.raises(NotImplementedError):
         GradScaler().step(torch.optim.SGD(model.parameters(), 1e-4, momentum=0.9))
+
+
+def test_checkpoint_save_load_resume_is_bit_exact(tmp_path):
+    """the reference only saves (`ddp_main.py:165-169`); loading the same dict back into a fresh
+    model + scaler and continuing must give exactly the run that never stopped.  The file is the reference's format:
+    {"model": DDP state_dict with `module.` keys, "scaler": GradScaler.state_dict()}."""
+    from ddp_practice_b200.shim import GradScaler, nn
+
+    def build(seed):
+        torch.manual_seed(seed)
+        m = nn.parallel.DistributedDataParallel(
+            nn.SyncBatchNorm.convert_sync_batchnorm(RefConvNet(torch.float16, "cuda").cuda()), device_ids=[0])
+        return m, nn.CrossEntropyLoss().cuda(), torch.optim.SGD(m.parameters(), 1e-4), GradScaler(growth_interval=3)
+
+    x, y = O.synthetic_mnist(32 * 8)
+    batches = [(x[i * 32:(i + 1) * 32], y[i * 32:(i + 1) * 32]) for i in range(8)]
+    # uninterrupted: 8 steps
+    m0, c0, o0, s0 = build(3407)
+    _reference_style_loop(m0, batches, c0, o0, s0)
+    # interrupted after 4 steps, saved, loaded into objects built from another seed, 4 more steps
+    m1, c1, o1, s1 = build(3407)
+    _reference_style_loop(m1, batches[:4], c1, o1, s1)
+    path = str(tmp_path / "ddp_checkpoint.pt")
+    torch.save({"model": m1.state_dict(), "scaler": s1.state_dict()}, path)
+    ck = torch.load(path)
+    assert set(ck) == {"model", "scaler"} and len(ck["model"]) == 16 and all(k.startswith("module.") for k in ck["model"])
+    assert set(ck["scaler"]) == {"scale", "growth_factor", "backoff_factor", "growth_interval", "_growth_tracker"}
+    m2, c2, o2, s2 = build(1)
+    m2.load_state_dict(ck["model"])
+    s2.load_state_dict(ck["scaler"])
+    _reference_style_loop(m2, batches[4:], c2, o2, s2)
+    torch.cuda.synchronize()
+    assert torch.equal(flat_params(m2), flat_params(m0))
+    assert torch.equal(bn_buffers(m2), bn_buffers(m0))
+    assert s2.state_dict() == s0.state_dict()
+    assert m2.state_dict()["module.layer1.1.num_batches_tracked"].item() == 8
+    # and the file loads into the plain torch model the reference would use
+    ref = RefConvNet(torch.float16, "cuda")
+    ref.load_state_dict({k.removeprefix("module."): v.cpu() for k, v in ck["model"].items()})
