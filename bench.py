@@ -244,6 +244,24 @@ def main():
     barrier()
     e2e_ms = max_over_ranks(e0.elapsed_time(e1))
 
+    # ---- the input pipeline fused in -- resident uint8 dataset + DistributedSampler indices
+    from torch.utils.data.distributed import DistributedSampler
+    u8 = (x_all * 255).round().to(torch.uint8).cuda()
+    sampler = DistributedSampler(range(n_local), num_replicas=1, rank=0)
+    sampler.set_epoch(0)
+    order = torch.tensor(list(iter(sampler)), dtype=torch.int64).cuda()
+    idx_batches = [order[j * B:(j + 1) * B].contiguous() for j in range(nb)]
+    for i in range(W):
+        eng.train_step_indexed(u8, yd, idx_batches[i % nb])
+    barrier()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    for i in range(K):
+        eng.train_step_indexed(u8, yd, idx_batches[(W + i) % nb])
+    p1.record()
+    barrier()
+    pipe_ms = max_over_ranks(p0.elapsed_time(p1))
+
     # ---- per-kernel device times (graph with event nodes), for the roofline of the dominant kernel
     prof = {}
     n_prof = 20
@@ -280,7 +298,10 @@ def main():
             "e2e": {"value": world * B * k_e2e / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * 784 * 4 + B * 8,
                     "d2h_bytes_per_step": 4, "steps": k_e2e, "ms_per_step": e2e_ms / k_e2e,
                     "api": "ddpstep_train_step_host: pinned host batch copied in, loss returned through a pinned mailbox, every step"},
-            "gpu_launches": gpu_launches, "roofline": roof}
+            "gpu_launches": gpu_launches, "roofline": roof,
+            "input_pipeline": {"value": world * B * K / (pipe_ms * 1e-3), "unit": UNIT, "ms_per_step": pipe_ms / K,
+                               "what": "same step fed from a GPU-resident uint8 dataset by DistributedSampler indices; "
+                                       "gather and ToTensor's /255 fused into conv1's load (ddpstep_train_step_indexed)"}}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         b = cpu_reference_run(B, steps=3000, warmup=30, budget_s=12.0)
         line["cpu_baseline"] = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -43,6 +43,8 @@ SYMBOLS = [
     ("ddpstep_state_ptrs", C.c_int, [_P, C.POINTER(Ptrs)]),
     ("ddpstep_train_step", C.c_int, [_P, _P, _P, C.c_int32, _P]),
     ("ddpstep_train_step_host", C.c_int, [_P, _P, _P, C.c_int32, _P, _P]),
+    ("ddpstep_train_step_indexed", C.c_int, [_P, _P, _P, _P, C.c_int32, _P]),
+    ("ddpstep_eval_batch_indexed", C.c_int, [_P, _P, _P, _P, C.c_int32, _P]),
     ("ddpstep_eval_batch", C.c_int, [_P, _P, _P, C.c_int32, _P]),
     ("ddpstep_reset_counts", C.c_int, [_P, _P]),
     ("ddpstep_reduce_counts", C.c_int, [_P, _P]),

@@ -31,7 +31,7 @@ struct GraphEntry {
   Conv1Args a_c1;
   FcArgs a_fc;
   Conv1WgradArgs a_c1w;
-  const float* x = nullptr;
+  BatchSrc x = {nullptr, nullptr, nullptr};
   const int64_t* y = nullptr;
   int n_kernels = 0;
 };
@@ -326,7 +326,7 @@ static void launch_k(void (*kernel)(A), dim3 grid, dim3 block, size_t smem, cuda
 }
 
 template <typename T>
-static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
+static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
   const ddpstep_config& cfg = c->cfg;
   const int dbl = cfg.conv_bias_double_round, sync = cfg.sync_bn;
   BnStat* st1 = c->st;
@@ -400,7 +400,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
                 defer2 ? c->part2 : nullptr, tc ? g2 * tsplit : g2};
   launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark();
   // 5. Linear + CE + dlogits + d(pool2 out)
-  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, c->dlogits, c->dflat, c->nll, c->counts,
+  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, c->dlogits, c->dflat, c->nll, c->counts,
            c->ds, B, cfg.use_scaler, 0};
   if (rec) rec->a_fc = f;
   launch_k(k_fc_ce<T>, dim3(std::min(B, 296)), dim3(224), 0, s, f, pdl); mark();
@@ -473,7 +473,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const float* x, const int64_t* 
 }
 
 template <typename T>
-static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
+static cudaError_t enqueue_eval(ddpstep_ctx* c, const BatchSrc& x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
   const ddpstep_config& cfg = c->cfg;
   const int dbl = cfg.conv_bias_double_round;
   auto mark = [&]() {
@@ -518,14 +518,14 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const float* x, const int64_t* y
   mark();
   BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps, nullptr, 0};
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
-  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1};
+  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1};
   if (rec) rec->a_fc = f;
   k_fc_ce<T><<<std::min(B, 296), 224, 0, s>>>(f); mark();
   return cudaGetLastError();
 }
 
 template <bool TRAIN>
-static cudaError_t enqueue(ddpstep_ctx* c, const float* x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
+static cudaError_t enqueue(ddpstep_ctx* c, const BatchSrc& x, const int64_t* y, int B, cudaStream_t s, Recorder* rec) {
   switch (c->cfg.dtype) {
     case DDPSTEP_FP32: return TRAIN ? enqueue_train<float>(c, x, y, B, s, rec) : enqueue_eval<float>(c, x, y, B, s, rec);
     case DDPSTEP_FP16: return TRAIN ? enqueue_train<__half>(c, x, y, B, s, rec) : enqueue_eval<__half>(c, x, y, B, s, rec);
@@ -555,8 +555,8 @@ static int repoint(ddpstep_ctx* ctx, GraphEntry& ge, cudaGraphNode_t node, void*
 // One captured graph per (mode, batch).  The step is launch- and latency-bound at batch 32,
 // so the 13 kernels are replayed with a single cudaGraphLaunch.
 template <bool TRAIN>
-static int run_graph(ddpstep_ctx* ctx, const float* x, const int64_t* y, int B, cudaStream_t s) {
-  const long key = TRAIN ? (long)B : (y ? -(long)B : -(long)B - 100000);
+static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int B, cudaStream_t s) {
+  const long key = (TRAIN ? (long)B : (y ? -(long)B : -(long)B - 100000)) + (x.x == nullptr ? 10000000L : 0L);
   auto it = ctx->graphs.find(key);
   if (it == ctx->graphs.end()) {
     GraphEntry ge;
@@ -591,7 +591,7 @@ static int run_graph(ddpstep_ctx* ctx, const float* x, const int64_t* y, int B, 
     it = ctx->graphs.emplace(key, ge).first;
   }
   GraphEntry& ge = it->second;
-  if (ge.x != x) {
+  if (ge.x.x != x.x || ge.x.u8 != x.u8 || ge.x.idx != x.idx) {
     ge.a_c1.x = x;
     int rc = repoint(ctx, ge, ge.node_c1, &ge.a_c1);
     if (rc) return rc;
@@ -602,8 +602,9 @@ static int run_graph(ddpstep_ctx* ctx, const float* x, const int64_t* y, int B, 
     }
     ge.x = x;
   }
-  if (ge.y != y) {
+  if (ge.y != y || ge.a_fc.idx != x.idx) {
     ge.a_fc.y = reinterpret_cast<const long long*>(y);
+    ge.a_fc.idx = x.idx;
     int rc = repoint(ctx, ge, ge.node_fc, &ge.a_fc);
     if (rc) return rc;
     ge.y = y;
@@ -630,9 +631,52 @@ extern "C" int ddpstep_train_step(ddpstep_ctx* ctx, const float* x, const int64_
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   ctx->steps_enqueued++;
-  if (ctx->cfg.use_graph) return run_graph<true>(ctx, x, y, batch, s);
-  cudaError_t e = enqueue<true>(ctx, x, y, batch, s, nullptr);
+  const BatchSrc src{x, nullptr, nullptr};
+  if (ctx->cfg.use_graph) return run_graph<true>(ctx, src, y, batch, s);
+  cudaError_t e = enqueue<true>(ctx, src, y, batch, s, nullptr);
   if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+// SURVEY 8(f) N1, the step immediately before the hot path: torchvision MNIST -> ToTensor -> DataLoader -> .cuda()
+// (ddp_main.py:127-141,86-87) becomes: the uint8 dataset resident in HBM, the sampler's indices for this batch, and the
+// gather + `/ 255` fused into conv1's load.
+static int check_indexed(ddpstep_ctx* ctx, const void* images, const void* labels, const void* idx, int32_t batch) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  if (!images || !idx) return fail(ctx, DDPSTEP_E_ARG, "null dataset / index pointer");
+  if (reinterpret_cast<uintptr_t>(images) & 15) return fail(ctx, DDPSTEP_E_ARG, "the uint8 dataset must be 16-byte aligned");
+  if (batch < 1 || batch > ctx->cfg.batch_cap)
+    return fail(ctx, DDPSTEP_E_ARG, "batch %d outside [1, batch_cap=%d]", batch, ctx->cfg.batch_cap);
+  if (!ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "world > 1: call ddpstep_import_peers first");
+  (void)labels;
+  return 0;
+}
+
+extern "C" int ddpstep_train_step_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8, const int64_t* labels,
+                                          const int64_t* idx, int32_t batch, void* stream) {
+  int rc = check_indexed(ctx, images_u8, labels, idx, batch);
+  if (rc) return rc;
+  if (!labels) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  ctx->steps_enqueued++;
+  const BatchSrc src{nullptr, images_u8, reinterpret_cast<const long long*>(idx)};
+  if (ctx->cfg.use_graph) return run_graph<true>(ctx, src, labels, batch, s);
+  cudaError_t e = enqueue<true>(ctx, src, labels, batch, s, nullptr);
+  if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+extern "C" int ddpstep_eval_batch_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8, const int64_t* labels,
+                                          const int64_t* idx, int32_t batch, void* stream) {
+  int rc = check_indexed(ctx, images_u8, labels, idx, batch);
+  if (rc) return rc;
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const BatchSrc src{nullptr, images_u8, reinterpret_cast<const long long*>(idx)};
+  if (ctx->cfg.use_graph) return run_graph<false>(ctx, src, labels, batch, s);
+  cudaError_t e = enqueue<false>(ctx, src, labels, batch, s, nullptr);
+  if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "eval launch failed: %s", cudaGetErrorString(e));
   return 0;
 }
 
@@ -690,8 +734,9 @@ extern "C" int ddpstep_eval_batch(ddpstep_ctx* ctx, const float* x, const int64_
   if (rc) return rc;
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (ctx->cfg.use_graph) return run_graph<false>(ctx, x, y, batch, s);
-  cudaError_t e = enqueue<false>(ctx, x, y, batch, s, nullptr);
+  const BatchSrc src{x, nullptr, nullptr};
+  if (ctx->cfg.use_graph) return run_graph<false>(ctx, src, y, batch, s);
+  cudaError_t e = enqueue<false>(ctx, src, y, batch, s, nullptr);
   if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "eval launch failed: %s", cudaGetErrorString(e));
   return 0;
 }
@@ -785,7 +830,7 @@ extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int6
     const int64_t before = ctx->launches;
     CK(cudaStreamBeginCapture(ctx->cap_stream, cudaStreamCaptureModeThreadLocal));
     cudaEventRecordWithFlags(ev0, ctx->cap_stream, cudaEventRecordExternal);
-    e = enqueue<true>(ctx, x, y, batch, ctx->cap_stream, &rec);
+    e = enqueue<true>(ctx, BatchSrc{x, nullptr, nullptr}, y, batch, ctx->cap_stream, &rec);
     cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &graph);
     ctx->launches = before;
     if (e != cudaSuccess || e2 != cudaSuccess)
@@ -799,7 +844,7 @@ extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int6
   } else {
     rec.ev_stream = s;
     CK(cudaEventRecord(ev0, s));
-    e = enqueue<true>(ctx, x, y, batch, s, &rec);
+    e = enqueue<true>(ctx, BatchSrc{x, nullptr, nullptr}, y, batch, s, &rec);
     if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "profile launch failed: %s", cudaGetErrorString(e));
     CK(cudaStreamSynchronize(s));
   }
@@ -887,7 +932,7 @@ extern "C" int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const floa
   CommDev comm;
   memset(&comm, 0, sizeof comm);
   comm.world = 1;
-  Conv1Args a{x_dev, params_dev, y1_dev, sc->part, 0, &sc->st, &sc->ds, comm, batch, conv_bias_double_round, 0, bn_eps};
+  Conv1Args a{BatchSrc{x_dev, nullptr, nullptr}, params_dev, y1_dev, sc->part, 0, &sc->st, &sc->ds, comm, batch, conv_bias_double_round, 0, bn_eps};
   switch (dtype) {
     case DDPSTEP_FP32: k_conv1_fwd<float><<<dim3(batch, C1_GROUPS), C1_THREADS, 0, s>>>(a); break;
     case DDPSTEP_FP16: k_conv1_fwd<__half><<<dim3(batch, C1_GROUPS), C1_THREADS, 0, s>>>(a); break;

@@ -416,7 +416,7 @@ __global__ void __launch_bounds__(160) k_conv2_wgrad(Conv2WgradArgs a) {
 // with a 5-wide kw register tile.
 struct Conv1WgradArgs {
   BnBwdArgs bn;    // y = y1, dpool = d(pool1 out), layer = 0
-  const float* x;  // [B,784] fp32
+  BatchSrc x;      // the input batch (same source as conv1 forward)
 };
 
 constexpr int C1W_THREADS = 160;
@@ -450,7 +450,7 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
   for (int n = blockIdx.x; n < a.bn.B; n += gridDim.x) {
     __syncthreads();
     for (int i = tid; i < 196; i += C1W_THREADS) {
-      const float4 v = __ldg(reinterpret_cast<const float4*>(a.x + (size_t)n * 784) + i);
+      const float4 v = load_pixels4(a.x, n, i);
       float* d = &xs[((4 * i) / 28 + 2) * C1_XS + (4 * i) % 28 + 2];
       d[0] = rnd<T>(v.x); d[1] = rnd<T>(v.y); d[2] = rnd<T>(v.z); d[3] = rnd<T>(v.w);
     }

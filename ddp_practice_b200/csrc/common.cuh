@@ -45,6 +45,23 @@ template <typename T> __device__ __forceinline__ float conv_out(float acc, float
   return rnd<T>((dbl ? rnd<T>(acc) : acc) + bias_r);
 }
 
+// ---- where a batch comes from ------------------------------------------------------------
+// Either fp32 images already gathered into a batch (x, ddp_main.py:86), or -- the input-pipeline
+// row of SURVEY 8(f) -- the whole dataset resident as uint8 [N,784] plus this batch's sampler
+// indices: the gather and ToTensor's `uint8 -> fp32, / 255` (transforms/functional.py:157) are
+// fused into the load, so no float batch ever exists in memory.
+struct BatchSrc {
+  const float* x;            // [B,784] fp32, or null
+  const unsigned char* u8;   // [N,784] uint8 dataset (used when x is null)
+  const long long* idx;      // [B] rows of the dataset (also indexes the labels), or null
+};
+// four consecutive pixels (i-th float4 of image n) as fp32
+__device__ __forceinline__ float4 load_pixels4(const BatchSrc& b, int n, int i) {
+  if (b.x != nullptr) return __ldg(reinterpret_cast<const float4*>(b.x + (size_t)n * 784) + i);
+  const uchar4 q = __ldg(reinterpret_cast<const uchar4*>(b.u8 + (size_t)b.idx[n] * 784) + i);
+  return make_float4((float)q.x / 255.0f, (float)q.y / 255.0f, (float)q.z / 255.0f, (float)q.w / 255.0f);
+}
+
 // ---- cross-GPU symmetric region (identical layout on every rank) -----------------------
 // Exchanges are PUSH and fence-free: every value travels as ONE naturally aligned 8-byte word
 // {fp32 payload, 32-bit epoch tag} stored straight into the consumer's memory over NVLink (an

@@ -106,7 +106,7 @@ __device__ void finalize_fwd_stats(const float* part, int rows, float count, flo
 // is staged once in shared memory, every output is written once with 8/16-byte stores, the BN
 // reduction rides in the epilogue.
 struct Conv1Args {
-  const float* x;
+  BatchSrc x;
   const float* params;
   void* y1;
   float* part;  // [gridDim.x][16][2]
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
   for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
     __syncthreads();
     for (int i = tid; i < 196; i += C1_THREADS) {  // 784 floats as 196 float4
-      const float4 v = __ldg(reinterpret_cast<const float4*>(a.x + (size_t)n * 784) + i);
+      const float4 v = load_pixels4(a.x, n, i);
       const int r = (4 * i) / 28, c = (4 * i) % 28;
       float* d = &xs[(r + 2) * C1_XS + c + 2];
       d[0] = rnd<T>(v.x); d[1] = rnd<T>(v.y); d[2] = rnd<T>(v.z); d[3] = rnd<T>(v.w);
@@ -545,6 +545,7 @@ struct FcArgs {
   const void* p2;        // [B,1568]
   const float* params;
   const long long* y;    // labels (may be null in eval)
+  const long long* idx;  // null, or this batch's dataset rows: label of image n is y[idx[n]]
   void* logits;          // [B,10] T
   void* dlogits;         // [B,10] T          (train)
   void* dflat;           // [B,1568] T        (train)  d(pool2 out)
@@ -607,7 +608,7 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
 #pragma unroll
         for (int j = 1; j < 10; ++j)
           if (lg[j] > best || (lg[j] != lg[j] && best == best)) { best = lg[j]; arg = j; }
-        if ((long long)arg == a.y[n]) atomicAdd(&a.counts[0], 1.0f);
+        if ((long long)arg == a.y[a.idx ? a.idx[n] : n]) atomicAdd(&a.counts[0], 1.0f);
         atomicAdd(&a.counts[1], 1.0f);
       }
       __syncthreads();
@@ -617,7 +618,7 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
 #pragma unroll
     for (int j = 0; j < 10; ++j) se += expf(lg[j] - mx);
     const float lse = logf(se);
-    const int label = (int)a.y[n];
+    const int label = (int)a.y[a.idx ? a.idx[n] : n];
     float dl[10], nll = 0.f;
 #pragma unroll
     for (int j = 0; j < 10; ++j) {

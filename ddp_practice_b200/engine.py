@@ -153,6 +153,22 @@ class Engine:
             self._check(rc)
         return loss.value if want_loss else None
 
+    def train_step_indexed(self, images_u8: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor):
+        """Input-pipeline form: resident uint8 dataset [N,1,28,28] / [N,784], labels [N] int64, and this batch's
+        sampler indices [B] int64 (all on the GPU).  Gather and ToTensor's /255 are fused into conv1's load."""
+        assert images_u8.is_cuda and images_u8.dtype == torch.uint8 and images_u8.is_contiguous()
+        assert labels.is_cuda and labels.dtype == torch.int64 and idx.is_cuda and idx.dtype == torch.int64
+        assert idx.is_contiguous() and labels.is_contiguous()
+        self._check(self.lib.ddpstep_train_step_indexed(self.ctx, images_u8.data_ptr(), labels.data_ptr(), idx.data_ptr(),
+                                                        idx.shape[0], self._stream()))
+
+    def eval_batch_indexed(self, images_u8: torch.Tensor, labels: Optional[torch.Tensor], idx: torch.Tensor) -> torch.Tensor:
+        assert images_u8.is_cuda and images_u8.dtype == torch.uint8 and idx.is_cuda and idx.dtype == torch.int64
+        self._check(self.lib.ddpstep_eval_batch_indexed(self.ctx, images_u8.data_ptr(),
+                                                        None if labels is None else labels.data_ptr(), idx.data_ptr(),
+                                                        idx.shape[0], self._stream()))
+        return self.logits[: idx.shape[0]]
+
     def eval_batch(self, x: torch.Tensor, y: Optional[torch.Tensor] = None) -> torch.Tensor:
         assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
         if y is not None:

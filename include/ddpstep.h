@@ -117,6 +117,17 @@ int ddpstep_train_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_de
 int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* x_host, const int64_t* y_host,
                             int32_t batch, float* loss_out, void* stream);
 
+/* The input pipeline in front of the step: instead of torchvision MNIST -> ToTensor ->
+ * DataLoader workers -> pinned batch -> `.cuda()` (ddp_main.py:127-141, 86-87), the dataset stays in HBM as
+ * the uint8 bytes MNIST consists of, images_u8_dev [N,784] and labels_dev [N], and a step receives the
+ * DistributedSampler's indices for this batch, idx_dev [batch] (torch/utils/data/distributed.py:107-141).
+ * The gather and ToTensor's `uint8 -> fp32, / 255` (torchvision/transforms/functional.py:157) happen inside
+ * conv1's load.  Same arithmetic, bit for bit, as ddpstep_train_step on images_u8[idx].float() / 255.        */
+int ddpstep_train_step_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8_dev, const int64_t* labels_dev,
+                               const int64_t* idx_dev, int32_t batch, void* stream);
+int ddpstep_eval_batch_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8_dev, const int64_t* labels_dev,
+                               const int64_t* idx_dev, int32_t batch, void* stream);
+
 /* One iteration of test(): ddp_main.py:101-107.  Eval-mode forward (running statistics),
  * logits left in ptrs.logits; when y_dev != NULL also `size += batch` and
  * `correct += (argmax == y).sum()` into ptrs.counts.                                        */
