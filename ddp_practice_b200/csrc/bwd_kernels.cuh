@@ -102,17 +102,40 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
   pdl_sync();  // predecessor produced dpool; the statistics above come from an earlier kernel
   float sdy = 0.f, sdyx = 0.f;
   const int total = max(0, n1 - n0) * HP * HP;
-#pragma unroll 4
-  for (int e = tid; e < total; e += 256) {
-    const int n = n0 + e / (HP * HP), w = e % (HP * HP), ph = w / HP, pw = w % HP;
+  // four windows per iteration, every load issued (unconditionally) before any is used: enough bytes in
+  // flight per thread to run at HBM speed at large batch
+  int e0 = tid;
+  for (; e0 + 768 < total; e0 += 1024) {
+    float v[4][4], d[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * 256;
+      const int n = n0 + e / (HP * HP), w = e % (HP * HP), ph = w / HP, pw = w % HP;
+      const T* src = y + (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
+      load2<T>(src, v[u][0], v[u][1]);
+      load2<T>(src + H, v[u][2], v[u][3]);
+      d[u] = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      bool live;
+      const int arg = pool_winner<T>(v[u], mu, is, g, b, live);
+      if (live) {
+        sdy += d[u];
+        sdyx = fmaf(d[u], v[u][arg] - mu, sdyx);
+      }
+    }
+  }
+  for (; e0 < total; e0 += 256) {  // remainder (and the whole loop at small batch): one window at a time
+    const int n = n0 + e0 / (HP * HP), w = e0 % (HP * HP), ph = w / HP, pw = w % HP;
     const T* src = y + (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
     float v[4];
     load2<T>(src, v[0], v[1]);
     load2<T>(src + H, v[2], v[3]);
+    const float d = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
     bool live;
     const int arg = pool_winner<T>(v, mu, is, g, b, live);
     if (live) {
-      const float d = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
       sdy += d;
       sdyx = fmaf(d, v[arg] - mu, sdyx);
     }

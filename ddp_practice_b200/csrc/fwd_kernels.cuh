@@ -358,15 +358,11 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   T* __restrict__ p = reinterpret_cast<T*>(a.p);
   const size_t total = (size_t)a.B * C * HP * HP;
-#pragma unroll 4
-  for (size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (size_t)gridDim.x * 256) {
+  const size_t stride = (size_t)gridDim.x * 256;
+  auto emit = [&](size_t idx, float v0, float v1, float v2, float v3) {
     const int pw = (int)(idx % HP), ph = (int)((idx / HP) % HP);
     const size_t plane = idx / (HP * HP);
     const int c = (int)(plane % C);
-    const T* src = y + (plane * H + 2 * ph) * H + 2 * pw;
-    float v0, v1, v2, v3;
-    load2<T>(src, v0, v1);
-    load2<T>(src + H, v2, v3);
     const float mu = s_mean[c], is = s_invstd[c], g = s_g[c], b = s_b[c];
     v0 = rnd<T>((v0 - mu) * is * g + b);
     v1 = rnd<T>((v1 - mu) * is * g + b);
@@ -378,6 +374,28 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
       const int n = (int)(plane / C);
       stf<T>(reinterpret_cast<T*>(a.p_planes) + (((size_t)(n * 2 + (c >> 3)) * 320 + (ph + 3) * 16 + pw) * 8 + (c & 7)), m);
     }
+  };
+  size_t idx0 = (size_t)blockIdx.x * 256 + threadIdx.x;
+  for (; idx0 + 3 * stride < total; idx0 += 4 * stride) {  // large batch: four outputs per iteration, loads first
+    float vv[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t idx = idx0 + u * stride;
+      const int pw = (int)(idx % HP), ph = (int)((idx / HP) % HP);
+      const T* src = y + ((idx / (HP * HP)) * H + 2 * ph) * H + 2 * pw;
+      load2<T>(src, vv[u][0], vv[u][1]);
+      load2<T>(src + H, vv[u][2], vv[u][3]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) emit(idx0 + u * stride, vv[u][0], vv[u][1], vv[u][2], vv[u][3]);
+  }
+  for (; idx0 < total; idx0 += stride) {
+    const int pw = (int)(idx0 % HP), ph = (int)((idx0 / HP) % HP);
+    const T* src = y + ((idx0 / (HP * HP)) * H + 2 * ph) * H + 2 * pw;
+    float v0, v1, v2, v3;
+    load2<T>(src, v0, v1);
+    load2<T>(src + H, v2, v3);
+    emit(idx0, v0, v1, v2, v3);
   }
   if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 15);
 }
