@@ -14,6 +14,7 @@
 
 #include "bwd_kernels.cuh"
 #include "conv2_tc.cuh"
+#include "conv1_tc.cuh"
 #include "fwd_kernels.cuh"
 #include "step_kernel.cuh"
 
@@ -31,6 +32,8 @@ struct GraphEntry {
   Conv1Args a_c1;
   FcArgs a_fc;
   Conv1WgradArgs a_c1w;
+  Conv1TcArgs a_c1tc;
+  bool c1tc = false;  // the first input-consuming node is the tensor-core conv1 (large batch)
   BatchSrc x = {nullptr, nullptr, nullptr};
   const int64_t* y = nullptr;
   int n_kernels = 0;
@@ -49,7 +52,7 @@ struct ddpstep_ctx {
   void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
   void *p1h = nullptr, *dy2h = nullptr, *w2_tiles = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
-  bool use_tc = false, use_wgrad_tc = false, use_pdl = true, last_planes = false;
+  bool use_tc = false, use_wgrad_tc = false, use_pdl = true, last_planes = false, use_conv1_tc = true;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   float* x_stage = nullptr;
   int64_t* y_stage = nullptr;
@@ -139,6 +142,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
+    const char* envc = getenv("DDPSTEP_CONV1_TC");
+    ctx->use_conv1_tc = !(envc && envc[0] == '0');
     const char* envp = getenv("DDPSTEP_PDL");
     ctx->use_pdl = !(envp && envp[0] == '0');
     const char* envw = getenv("DDPSTEP_WGRAD_TC");
@@ -170,6 +175,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__nv_bfloat16, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1T_SMEM);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1T_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
@@ -310,6 +317,8 @@ struct Recorder {  // keeps the argument structs that hold x / y so graph replay
   Conv1Args a_c1;
   FcArgs a_fc;
   Conv1WgradArgs a_c1w;
+  Conv1TcArgs a_c1tc;
+  bool c1tc = false;
 };
 
 // Kernel launch with an optional programmatic (PDL) edge to the previous kernel of the stream:
@@ -365,10 +374,22 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   const int defer1 = g1 <= 64, defer2 = std::min(B, 148) <= 64;
   Conv1Args a1{x, c->params, c->y1, c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
-  k_conv1_fwd<T><<<dim3(g1, C1_GROUPS), C1_THREADS, 0, s>>>(a1); mark();
+  bool c1tc = false;
+  int rows1 = g1;
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c->use_tc && c->use_conv1_tc && B > 64) {  // large batch: conv1 on the tensor cores (conv1_tc.cuh)
+      c1tc = true;
+      rows1 = std::min(B, 148);
+      Conv1TcArgs t1{x, c->params, c->y1, c->part1, 0, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+      if (rec) { rec->a_c1tc = t1; rec->c1tc = true; }
+      k_conv1_tc<T><<<rows1, C1T_THREADS, C1T_SMEM, s>>>(t1);
+    }
+  }
+  if (!c1tc) k_conv1_fwd<T><<<dim3(g1, C1_GROUPS), C1_THREADS, 0, s>>>(a1);
+  mark();
   // 2. BN1 + ReLU + pool
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps,
-                defer1 ? c->part1 : nullptr, g1};
+                defer1 ? c->part1 : nullptr, rows1};
   bool planes = false;
   // large batches: write p1 / d(conv2 out) only as padded planes with 16-byte stores (nobody reads the NCHW copies);
   // small batches keep the one-thread-per-element kernels, whose shorter per-thread chains give lower latency
@@ -533,12 +554,12 @@ static cudaError_t enqueue(ddpstep_ctx* c, const BatchSrc& x, const int64_t* y, 
   }
 }
 
-struct KernelPtrs { const void *c1, *fc, *c1w; };
+struct KernelPtrs { const void *c1, *fc, *c1w, *c1tc; };
 static KernelPtrs kernel_ptrs(int dtype) {
   switch (dtype) {
-    case DDPSTEP_FP32: return {(const void*)k_conv1_fwd<float>, (const void*)k_fc_ce<float>, (const void*)k_conv1_wgrad<float>};
-    case DDPSTEP_FP16: return {(const void*)k_conv1_fwd<__half>, (const void*)k_fc_ce<__half>, (const void*)k_conv1_wgrad<__half>};
-    default: return {(const void*)k_conv1_fwd<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16>, (const void*)k_conv1_wgrad<__nv_bfloat16>};
+    case DDPSTEP_FP32: return {(const void*)k_conv1_fwd<float>, (const void*)k_fc_ce<float>, (const void*)k_conv1_wgrad<float>, nullptr};
+    case DDPSTEP_FP16: return {(const void*)k_conv1_fwd<__half>, (const void*)k_fc_ce<__half>, (const void*)k_conv1_wgrad<__half>, (const void*)k_conv1_tc<__half>};
+    default: return {(const void*)k_conv1_fwd<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16>, (const void*)k_conv1_wgrad<__nv_bfloat16>, (const void*)k_conv1_tc<__nv_bfloat16>};
   }
 }
 
@@ -581,19 +602,21 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
       cudaKernelNodeParams p;
       CK(cudaGraphKernelNodeGetParams(nd, &p));
       if (p.func == kp.c1) ge.node_c1 = nd;
+      else if (kp.c1tc && p.func == kp.c1tc) { ge.node_c1 = nd; ge.c1tc = true; }
       else if (p.func == kp.fc) ge.node_fc = nd;
       else if (p.func == kp.c1w) ge.node_c1w = nd;
     }
     if (!ge.node_c1 || !ge.node_fc || (TRAIN && !ge.node_c1w))
       return fail(ctx, DDPSTEP_E_STATE, "could not locate the input-consuming kernel nodes in the captured graph");
-    ge.a_c1 = rec.a_c1; ge.a_fc = rec.a_fc; ge.a_c1w = rec.a_c1w;
+    ge.a_c1 = rec.a_c1; ge.a_fc = rec.a_fc; ge.a_c1w = rec.a_c1w; ge.a_c1tc = rec.a_c1tc;
     ge.x = x; ge.y = y; ge.n_kernels = rec.n;
     it = ctx->graphs.emplace(key, ge).first;
   }
   GraphEntry& ge = it->second;
   if (ge.x.x != x.x || ge.x.u8 != x.u8 || ge.x.idx != x.idx) {
     ge.a_c1.x = x;
-    int rc = repoint(ctx, ge, ge.node_c1, &ge.a_c1);
+    ge.a_c1tc.x = x;
+    int rc = ge.c1tc ? repoint(ctx, ge, ge.node_c1, &ge.a_c1tc) : repoint(ctx, ge, ge.node_c1, &ge.a_c1);
     if (rc) return rc;
     if (TRAIN) {
       ge.a_c1w.x = x;
