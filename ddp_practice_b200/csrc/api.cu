@@ -34,6 +34,8 @@ struct GraphEntry {
   Conv1WgradArgs a_c1w;
   Conv1TcArgs a_c1tc;
   bool c1tc = false;  // the first input-consuming node is the tensor-core conv1 (large batch)
+  Conv1WgradTcArgs a_c1wtc;
+  bool c1wtc = false;
   BatchSrc x = {nullptr, nullptr, nullptr};
   const int64_t* y = nullptr;
   int n_kernels = 0;
@@ -52,7 +54,7 @@ struct ddpstep_ctx {
   void *y1 = nullptr, *p1 = nullptr, *y2 = nullptr, *p2 = nullptr, *logits = nullptr, *dlogits = nullptr;
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
   void *p1h = nullptr, *dy2h = nullptr, *w2_tiles = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
-  bool use_tc = false, use_wgrad_tc = false, use_pdl = true, last_planes = false, use_conv1_tc = true;
+  bool use_tc = false, use_wgrad_tc = false, use_pdl = true, last_planes = false, use_conv1_tc = true, use_conv1_wgrad_tc = true;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   float* x_stage = nullptr;
   int64_t* y_stage = nullptr;
@@ -142,6 +144,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
+    const char* envcw = getenv("DDPSTEP_CONV1_WGRAD_TC");
+    ctx->use_conv1_wgrad_tc = !(envcw && envcw[0] == '0');
     const char* envc = getenv("DDPSTEP_CONV1_TC");
     ctx->use_conv1_tc = !(envc && envc[0] == '0');
     const char* envp = getenv("DDPSTEP_PDL");
@@ -175,6 +179,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__nv_bfloat16, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1W_TC_SMEM);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1W_TC_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1T_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1T_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
@@ -319,6 +325,8 @@ struct Recorder {  // keeps the argument structs that hold x / y so graph replay
   Conv1WgradArgs a_c1w;
   Conv1TcArgs a_c1tc;
   bool c1tc = false;
+  Conv1WgradTcArgs a_c1wtc;
+  bool c1wtc = false;
 };
 
 // Kernel launch with an optional programmatic (PDL) edge to the previous kernel of the stream:
@@ -484,10 +492,22 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   const int gc1 = std::min(B, 296);
   Conv1WgradArgs cw{r1, x};
   if (rec) rec->a_c1w = cw;
-  launch_k(k_conv1_wgrad<T>, dim3(gc1, 4), dim3(C1W_THREADS), 0, s, cw, pdl); mark();
+  int rows_c1 = gc1;
+  bool c1wtc = false;
+  if constexpr (!std::is_same<T, float>::value) {
+    if (c1tc && c->use_conv1_wgrad_tc) {  // large batch: tensor-core weight gradient (conv1_tc.cuh)
+      c1wtc = true;
+      rows_c1 = std::min(B, 296);  // two CTAs per SM: the builders are latency-bound, a second CTA hides it
+      Conv1WgradTcArgs cwt{r1, x};
+      if (rec) { rec->a_c1wtc = cwt; rec->c1wtc = true; }
+      launch_k(k_conv1_wgrad_tc<T>, dim3(rows_c1), dim3(C1W_TC_THREADS), C1W_TC_SMEM, s, cwt, pdl);
+    }
+  }
+  if (!c1wtc) launch_k(k_conv1_wgrad<T>, dim3(gc1, 4), dim3(C1W_THREADS), 0, s, cw, pdl);
+  mark();
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->host_mail, c->bnbuf, c->nbt, c->ds, c->comm, B,
-              gc1, gw_rows, planes ? ns2p : ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
+              rows_c1, gw_rows, planes ? ns2p : ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();
   return cudaGetLastError();
@@ -554,12 +574,12 @@ static cudaError_t enqueue(ddpstep_ctx* c, const BatchSrc& x, const int64_t* y, 
   }
 }
 
-struct KernelPtrs { const void *c1, *fc, *c1w, *c1tc; };
+struct KernelPtrs { const void *c1, *fc, *c1w, *c1tc, *c1wtc; };
 static KernelPtrs kernel_ptrs(int dtype) {
   switch (dtype) {
-    case DDPSTEP_FP32: return {(const void*)k_conv1_fwd<float>, (const void*)k_fc_ce<float>, (const void*)k_conv1_wgrad<float>, nullptr};
-    case DDPSTEP_FP16: return {(const void*)k_conv1_fwd<__half>, (const void*)k_fc_ce<__half>, (const void*)k_conv1_wgrad<__half>, (const void*)k_conv1_tc<__half>};
-    default: return {(const void*)k_conv1_fwd<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16>, (const void*)k_conv1_wgrad<__nv_bfloat16>, (const void*)k_conv1_tc<__nv_bfloat16>};
+    case DDPSTEP_FP32: return {(const void*)k_conv1_fwd<float>, (const void*)k_fc_ce<float>, (const void*)k_conv1_wgrad<float>, nullptr, nullptr};
+    case DDPSTEP_FP16: return {(const void*)k_conv1_fwd<__half>, (const void*)k_fc_ce<__half>, (const void*)k_conv1_wgrad<__half>, (const void*)k_conv1_tc<__half>, (const void*)k_conv1_wgrad_tc<__half>};
+    default: return {(const void*)k_conv1_fwd<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16>, (const void*)k_conv1_wgrad<__nv_bfloat16>, (const void*)k_conv1_tc<__nv_bfloat16>, (const void*)k_conv1_wgrad_tc<__nv_bfloat16>};
   }
 }
 
@@ -605,10 +625,11 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
       else if (kp.c1tc && p.func == kp.c1tc) { ge.node_c1 = nd; ge.c1tc = true; }
       else if (p.func == kp.fc) ge.node_fc = nd;
       else if (p.func == kp.c1w) ge.node_c1w = nd;
+      else if (kp.c1wtc && p.func == kp.c1wtc) { ge.node_c1w = nd; ge.c1wtc = true; }
     }
     if (!ge.node_c1 || !ge.node_fc || (TRAIN && !ge.node_c1w))
       return fail(ctx, DDPSTEP_E_STATE, "could not locate the input-consuming kernel nodes in the captured graph");
-    ge.a_c1 = rec.a_c1; ge.a_fc = rec.a_fc; ge.a_c1w = rec.a_c1w; ge.a_c1tc = rec.a_c1tc;
+    ge.a_c1 = rec.a_c1; ge.a_fc = rec.a_fc; ge.a_c1w = rec.a_c1w; ge.a_c1tc = rec.a_c1tc; ge.a_c1wtc = rec.a_c1wtc;
     ge.x = x; ge.y = y; ge.n_kernels = rec.n;
     it = ctx->graphs.emplace(key, ge).first;
   }
@@ -620,7 +641,8 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
     if (rc) return rc;
     if (TRAIN) {
       ge.a_c1w.x = x;
-      rc = repoint(ctx, ge, ge.node_c1w, &ge.a_c1w);
+      ge.a_c1wtc.x = x;
+      rc = ge.c1wtc ? repoint(ctx, ge, ge.node_c1w, &ge.a_c1wtc) : repoint(ctx, ge, ge.node_c1w, &ge.a_c1w);
       if (rc) return rc;
     }
     ge.x = x;
