@@ -138,7 +138,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   A(y1, B * 16 * 784 * es); A(p1, B * 16 * 196 * es); A(y2, B * 32 * 196 * es); A(p2, B * 1568 * es);
   A(logits, B * 10 * es); A(dlogits, B * 10 * es); A(dflat, B * 1568 * es); A(dy2, B * 32 * 196 * es);
   A(dp1, B * 16 * 196 * es); A(nll, B * 4);
-  A(part1, 296 * 16 * 2 * 4); A(part2, 148 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
+  A(part1, 296 * 16 * 2 * 4); A(part2, 296 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
   A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
   A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4);
   {
@@ -379,7 +379,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   const int g1 = std::min(B, 296);
   // small grids: the BN kernels reduce the conv kernels' partial sums themselves (no last-CTA tail)
   const int tsplit = B <= 64 ? 2 : 1;  // tcgen05 conv2: one M-tile per CTA at small batch
-  const int defer1 = g1 <= 64, defer2 = std::min(B, 148) <= 64;
+  const int defer1 = g1 <= 64, defer2 = std::min(B, 296) <= 64;
   Conv1Args a1{x, c->params, c->y1, c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   if (rec) rec->a_c1 = a1;
   bool c1tc = false;
@@ -387,7 +387,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc && c->use_conv1_tc && B > 64) {  // large batch: conv1 on the tensor cores (conv1_tc.cuh)
       c1tc = true;
-      rows1 = std::min(B, 148);
+      rows1 = std::min(B, 296);  // two CTAs per SM
       Conv1TcArgs t1{x, c->params, c->y1, c->part1, 0, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
       if (rec) { rec->a_c1tc = t1; rec->c1tc = true; }
       k_conv1_tc<T><<<rows1, C1T_THREADS, C1T_SMEM, s>>>(t1);
@@ -411,7 +411,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   }
   mark();
   // 3. conv2 + local BN2 statistics
-  const int g2 = std::min(B, 148);
+  const int g2 = std::min(B, 296);  // tensor-core path: up to two CTAs per SM
   Conv14Args a2{c->p1, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   bool tc = false;
   if constexpr (!std::is_same<T, float>::value) {
@@ -432,7 +432,9 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, c->dlogits, c->dflat, c->nll, c->counts,
            c->ds, B, cfg.use_scaler, 0};
   if (rec) rec->a_fc = f;
-  launch_k(k_fc_ce<T>, dim3(std::min(B, 296)), dim3(224), 0, s, f, pdl); mark();
+  if (B > 1184) launch_k(k_fc_ce<T, 4>, dim3(296), dim3(224), 0, s, f, pdl);
+  else launch_k(k_fc_ce<T, 1>, dim3(std::min(B, 296)), dim3(224), 0, s, f, pdl);
+  mark();
   // 6. fc weight/bias gradient partials
   const int nsf = clampi(cdiv(B, 8), 1, 40);
   FcWgradArgs fw{c->p2, c->dlogits, c->gpart, B, cdiv(B, nsf)};
@@ -464,7 +466,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
     if (c->use_tc) {
       tc = true;
       Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
-      launch_k(k_conv2_tc<T, 2>, dim3(std::min(B, 148), tsplit), dim3(TC_THREADS), tc_smem_bytes(4), s, t2, pdl);
+      launch_k(k_conv2_tc<T, 2>, dim3(std::min(B, 296), tsplit), dim3(TC_THREADS), tc_smem_bytes(4), s, t2, pdl);
     }
   }
   if (!tc) k_conv14<T, 32, 16, 2><<<dim3(std::min(B, 296), 2), 128, (32 * 18 * C14_RS + 8 * 32 * 25) * 4, s>>>(d2);
@@ -561,7 +563,9 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const BatchSrc& x, const int64_t
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1};
   if (rec) rec->a_fc = f;
-  k_fc_ce<T><<<std::min(B, 296), 224, 0, s>>>(f); mark();
+  if (B > 1184) k_fc_ce<T, 4><<<296, 224, 0, s>>>(f);
+  else k_fc_ce<T, 1><<<std::min(B, 296), 224, 0, s>>>(f);
+  mark();
   return cudaGetLastError();
 }
 
@@ -574,12 +578,12 @@ static cudaError_t enqueue(ddpstep_ctx* c, const BatchSrc& x, const int64_t* y, 
   }
 }
 
-struct KernelPtrs { const void *c1, *fc, *c1w, *c1tc, *c1wtc; };
+struct KernelPtrs { const void *c1, *fc, *c1w, *c1tc, *c1wtc, *fc4; };
 static KernelPtrs kernel_ptrs(int dtype) {
   switch (dtype) {
-    case DDPSTEP_FP32: return {(const void*)k_conv1_fwd<float>, (const void*)k_fc_ce<float>, (const void*)k_conv1_wgrad<float>, nullptr, nullptr};
-    case DDPSTEP_FP16: return {(const void*)k_conv1_fwd<__half>, (const void*)k_fc_ce<__half>, (const void*)k_conv1_wgrad<__half>, (const void*)k_conv1_tc<__half>, (const void*)k_conv1_wgrad_tc<__half>};
-    default: return {(const void*)k_conv1_fwd<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16>, (const void*)k_conv1_wgrad<__nv_bfloat16>, (const void*)k_conv1_tc<__nv_bfloat16>, (const void*)k_conv1_wgrad_tc<__nv_bfloat16>};
+    case DDPSTEP_FP32: return {(const void*)k_conv1_fwd<float>, (const void*)k_fc_ce<float, 1>, (const void*)k_conv1_wgrad<float>, nullptr, nullptr, (const void*)k_fc_ce<float, 4>};
+    case DDPSTEP_FP16: return {(const void*)k_conv1_fwd<__half>, (const void*)k_fc_ce<__half, 1>, (const void*)k_conv1_wgrad<__half>, (const void*)k_conv1_tc<__half>, (const void*)k_conv1_wgrad_tc<__half>, (const void*)k_fc_ce<__half, 4>};
+    default: return {(const void*)k_conv1_fwd<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16, 1>, (const void*)k_conv1_wgrad<__nv_bfloat16>, (const void*)k_conv1_tc<__nv_bfloat16>, (const void*)k_conv1_wgrad_tc<__nv_bfloat16>, (const void*)k_fc_ce<__nv_bfloat16, 4>};
   }
 }
 
@@ -623,7 +627,7 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
       CK(cudaGraphKernelNodeGetParams(nd, &p));
       if (p.func == kp.c1) ge.node_c1 = nd;
       else if (kp.c1tc && p.func == kp.c1tc) { ge.node_c1 = nd; ge.c1tc = true; }
-      else if (p.func == kp.fc) ge.node_fc = nd;
+      else if (p.func == kp.fc || p.func == kp.fc4) ge.node_fc = nd;
       else if (p.func == kp.c1w) ge.node_c1w = nd;
       else if (kp.c1wtc && p.func == kp.c1wtc) { ge.node_c1w = nd; ge.c1wtc = true; }
     }

@@ -39,7 +39,7 @@ struct Conv1TcArgs {
 };
 
 template <typename T>
-__global__ void __launch_bounds__(C1T_THREADS, 1) k_conv1_tc(Conv1TcArgs a) {
+__global__ void __launch_bounds__(C1T_THREADS, 2) k_conv1_tc(Conv1TcArgs a) {
   extern __shared__ __align__(128) unsigned char c1_smem[];
   unsigned char* xe_s = c1_smem;                                   // [2][1032][8] T
   T* r_s = reinterpret_cast<T*>(c1_smem + 2 * C1T_XE_BYTES);       // [2][1048] T

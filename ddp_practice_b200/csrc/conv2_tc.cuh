@@ -141,7 +141,7 @@ struct Conv2TcArgs {
 };
 
 template <typename T, int MODE>
-__global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_tc(Conv2TcArgs a) {
+__global__ void __launch_bounds__(TC_THREADS, 2) k_conv2_tc(Conv2TcArgs a) {
   if (threadIdx.x == 0) TRACE((MODE == 0 ? 3 : 10) * 16 + 0);
   constexpr int PLANES = MODE == 0 ? 2 : 4;   // input channel groups of 8
   constexpr int N = MODE == 0 ? 32 : 16;      // output channels

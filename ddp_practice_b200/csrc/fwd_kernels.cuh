@@ -573,10 +573,12 @@ struct FcArgs {
   int B, use_scaler, eval;
 };
 
-template <typename T>
+// NI = images per loop iteration: 1 at small batch (shortest chain), 4 at large batch (the two block-wide
+// synchronisations per iteration are shared by four images and four times as many loads are in flight).
+template <typename T, int NI>
 __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
   if (threadIdx.x == 0) TRACE(5 * 16 + 0);
-  __shared__ float red[7][10];
+  __shared__ float red[7][NI][10];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const T* __restrict__ p2 = reinterpret_cast<const T*>(a.p2);
   T* __restrict__ logits = reinterpret_cast<T*>(a.logits);
@@ -593,71 +595,80 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
   const float gl = a.use_scaler ? rnd<T>(a.ds->scale) : 1.0f;
   const float g = rnd<T>(-(gl / (float)a.B));
 
-  for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
-    float xk[7];
+  for (int n0 = blockIdx.x * NI; n0 < a.B; n0 += gridDim.x * NI) {
+    float xk[NI][7];
 #pragma unroll
-    for (int i = 0; i < 7; ++i) xk[i] = ldf<T>(&p2[(size_t)n * 1568 + tid + 224 * i]);
+    for (int u = 0; u < NI; ++u)
 #pragma unroll
-    for (int j = 0; j < 10; ++j) {
-      float acc = 0.f;
+      for (int i = 0; i < 7; ++i)
+        xk[u][i] = (n0 + u < a.B) ? ldf<T>(&p2[(size_t)(n0 + u) * 1568 + tid + 224 * i]) : 0.f;
 #pragma unroll
-      for (int i = 0; i < 7; ++i) acc = fmaf(xk[i], w[j][i], acc);
-      acc = warp_sum(acc);
-      if (lane == 0) red[warp][j] = acc;
-    }
+    for (int u = 0; u < NI; ++u)
+#pragma unroll
+      for (int j = 0; j < 10; ++j) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 7; ++i) acc = fmaf(xk[u][i], w[j][i], acc);
+        acc = warp_sum(acc);
+        if (lane == 0) red[warp][u][j] = acc;
+      }
     __syncthreads();
-    float lg[10], mx = -INFINITY;
 #pragma unroll
-    for (int j = 0; j < 10; ++j) {
-      float v = 0.f;
+    for (int u = 0; u < NI; ++u) {
+      const int n = n0 + u;
+      if (n >= a.B) break;
+      float lg[10], mx = -INFINITY;
 #pragma unroll
-      for (int q = 0; q < 7; ++q) v += red[q][j];
-      lg[j] = rnd<T>(v + b[j]);
-      mx = fmaxf(mx, lg[j]);
-    }
-    if (a.eval) {
+      for (int j = 0; j < 10; ++j) {
+        float v = 0.f;
+#pragma unroll
+        for (int q = 0; q < 7; ++q) v += red[q][u][j];
+        lg[j] = rnd<T>(v + b[j]);
+        mx = fmaxf(mx, lg[j]);
+      }
+      if (a.eval) {
+#pragma unroll
+        for (int j = 0; j < 10; ++j)
+          if (tid == j) stf<T>(&logits[(size_t)n * 10 + j], lg[j]);
+        if (tid == 0 && a.y != nullptr) {
+          // argmax: first maximum, NaN counts as the maximum
+          float best = lg[0];
+          int arg = 0;
+#pragma unroll
+          for (int j = 1; j < 10; ++j)
+            if (lg[j] > best || (lg[j] != lg[j] && best == best)) { best = lg[j]; arg = j; }
+          if ((long long)arg == a.y[a.idx ? a.idx[n] : n]) atomicAdd(&a.counts[0], 1.0f);
+          atomicAdd(&a.counts[1], 1.0f);
+        }
+        continue;
+      }
+      float se = 0.f;
+#pragma unroll
+      for (int j = 0; j < 10; ++j) se += expf(lg[j] - mx);
+      const float lse = logf(se);
+      const int label = (int)a.y[a.idx ? a.idx[n] : n];
+      float dl[10], nll = 0.f;
+#pragma unroll
+      for (int j = 0; j < 10; ++j) {
+        const float lsm = rnd<T>(lg[j] - mx - lse);
+        if (j == label) nll = -lsm;
+        dl[j] = rnd<T>((j == label ? g : 0.f) - expf(lsm) * g);
+      }
 #pragma unroll
       for (int j = 0; j < 10; ++j)
-        if (tid == j) stf<T>(&logits[(size_t)n * 10 + j], lg[j]);
-      if (tid == 0 && a.y != nullptr) {
-        // argmax: first maximum, NaN counts as the maximum
-        float best = lg[0];
-        int arg = 0;
+        if (tid == j) {
+          stf<T>(&logits[(size_t)n * 10 + j], lg[j]);
+          stf<T>(&reinterpret_cast<T*>(a.dlogits)[(size_t)n * 10 + j], dl[j]);
+        }
+      if (tid == 0) a.nll[n] = nll;
+      T* __restrict__ dflat = reinterpret_cast<T*>(a.dflat);
 #pragma unroll
-        for (int j = 1; j < 10; ++j)
-          if (lg[j] > best || (lg[j] != lg[j] && best == best)) { best = lg[j]; arg = j; }
-        if ((long long)arg == a.y[a.idx ? a.idx[n] : n]) atomicAdd(&a.counts[0], 1.0f);
-        atomicAdd(&a.counts[1], 1.0f);
+      for (int i = 0; i < 7; ++i) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 10; ++j) acc = fmaf(dl[j], w[j][i], acc);
+        stf<T>(&dflat[(size_t)n * 1568 + tid + 224 * i], acc);
       }
-      __syncthreads();
-      continue;
-    }
-    float se = 0.f;
-#pragma unroll
-    for (int j = 0; j < 10; ++j) se += expf(lg[j] - mx);
-    const float lse = logf(se);
-    const int label = (int)a.y[a.idx ? a.idx[n] : n];
-    float dl[10], nll = 0.f;
-#pragma unroll
-    for (int j = 0; j < 10; ++j) {
-      const float lsm = rnd<T>(lg[j] - mx - lse);
-      if (j == label) nll = -lsm;
-      dl[j] = rnd<T>((j == label ? g : 0.f) - expf(lsm) * g);
-    }
-#pragma unroll
-    for (int j = 0; j < 10; ++j)
-      if (tid == j) {
-        stf<T>(&logits[(size_t)n * 10 + j], lg[j]);
-        stf<T>(&reinterpret_cast<T*>(a.dlogits)[(size_t)n * 10 + j], dl[j]);
-      }
-    if (tid == 0) a.nll[n] = nll;
-    T* __restrict__ dflat = reinterpret_cast<T*>(a.dflat);
-#pragma unroll
-    for (int i = 0; i < 7; ++i) {
-      float acc = 0.f;
-#pragma unroll
-      for (int j = 0; j < 10; ++j) acc = fmaf(dl[j], w[j][i], acc);
-      stf<T>(&dflat[(size_t)n * 1568 + tid + 224 * i], acc);
     }
     __syncthreads();
   }
