@@ -39,5 +39,16 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     return LIB_PATH
 
 
+def build_tools() -> None:
+    """Microbenchmarks and the tracing build of the library under tools/ (not tracked; they travel to the GPU box)."""
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    tools = os.path.join(PKG, "..", "tools")
+    arch = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17"]
+    for src in ("microbench", "microbench_step"):
+        subprocess.run([nvcc, *arch, "-o", os.path.join(tools, src + ".bin"), os.path.join(tools, src + ".cu")], check=True)
+    subprocess.run([nvcc, *arch, "-Xcompiler", "-fPIC", "-shared", "-DDDPSTEP_TRACE", "-o",
+                    os.path.join(tools, "libddpstep_trace.so"), os.path.join(CSRC, "api.cu")], check=True)
+
+
 if __name__ == "__main__":
     print(build_library(force=True, verbose=True))
