@@ -100,6 +100,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
   const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
   const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G + c], b = a.params[OFF_BE + c];
   pdl_sync();  // predecessor produced dpool; the statistics above come from an earlier kernel
+  if (threadIdx.x == 0) TRACE((C == 32 ? 7 : 11) * 16 + 1);
   float sdy = 0.f, sdyx = 0.f;
   const int total = max(0, n1 - n0) * HP * HP;
   // four windows per iteration, every load issued (unconditionally) before any is used: enough bytes in
@@ -149,6 +150,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
     for (int w = 0; w < 8; ++w) v += red[w][tid];
     a.bpart[((size_t)c * gridDim.y + blockIdx.y) * 2 + tid] = v;
   }
+  if (threadIdx.x == 0) TRACE((C == 32 ? 7 : 11) * 16 + 15);
   if (a.defer) return;
   if (last_cta_done(&a.ds->ticket[2 + a.layer], gridDim.x * gridDim.y)) {
     const bool xchg = a.sync && a.comm.world > 1;
@@ -252,26 +254,42 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
   constexpr int C = 32, H = 14, HP = 7;
   __shared__ float s_k1[C], s_k2[C];
   __shared__ float red[8];
-  bn_backward_sums<C>(a, s_k1, s_k2);
-  if (threadIdx.x == 0) TRACE(9 * 16 + 1);
   const int tid = threadIdx.x, c = blockIdx.x;
   const int n0 = blockIdx.y * a.per_split, n1 = min(a.B, n0 + a.per_split);
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
   T* __restrict__ dy = reinterpret_cast<T*>(a.dy);
+  const int total = max(0, n1 - n0) * HP * HP;
+  // Everything this thread's first window needs except the two sums is older than the predecessor's
+  // predecessor (a kernel is only launched once every CTA of the one before it has passed ITS wait), so it is
+  // fetched before the wait inside bn_backward_sums: one trip to L2 for the sums and the data together
   const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G2 + c], b = a.params[OFF_BE2 + c];
+  float pv[4] = {0.f, 0.f, 0.f, 0.f}, pd = 0.f;
+  if (tid < total) {
+    const int n = n0 + tid / (HP * HP), w = tid % (HP * HP), ph = w / HP, pw = w % HP;
+    const size_t off = (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
+    load2<T>(y + off, pv[0], pv[1]);
+    load2<T>(y + off + H, pv[2], pv[3]);
+    pd = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
+  }
+  bn_backward_sums<C>(a, s_k1, s_k2);
+  if (threadIdx.x == 0) TRACE(9 * 16 + 1);
   const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
   float bsum = 0.f;
-  const int total = max(0, n1 - n0) * HP * HP;
   for (int e = tid; e < total; e += 256) {
     const int n = n0 + e / (HP * HP), w = e % (HP * HP), ph = w / HP, pw = w % HP;
     const size_t off = (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
-    float v[4];
-    load2<T>(y + off, v[0], v[1]);
-    load2<T>(y + off + H, v[2], v[3]);
+    float v[4], dd;
+    if (e == tid) {
+      v[0] = pv[0]; v[1] = pv[1]; v[2] = pv[2]; v[3] = pv[3]; dd = pd;
+    } else {
+      load2<T>(y + off, v[0], v[1]);
+      load2<T>(y + off + H, v[2], v[3]);
+      dd = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
+    }
     bool live;
     const int arg = pool_winner<T>(v, mu, is, g, b, live);
-    const float d = live ? ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]) : 0.f;
+    const float d = live ? dd : 0.f;
     float o[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -434,8 +452,8 @@ __global__ void __launch_bounds__(160) k_conv2_wgrad(Conv2WgradArgs a) {
 // BN1 backward pass 2 fused with the conv1 weight / bias gradient (conv1's input needs no
 // gradient, so d(conv1 out) lives only in shared memory):
 //   dW1[co][kh][kw] = sum_{n,h,w} dy1[n,co,h,w] * x[n,h+kh-2,w+kw-2],  db1[co] = sum dy1
-// CTA = one image x 4 channels (grid.y = 4), 160 threads.  Phase A: one pooling window per
-// thread-iteration -> dy1 in shared memory.  Phase B: thread = (channel, kh, 4 of the 28 rows)
+// CTA = one image x 4 channels (grid.y = 4), 160 threads.  Phase A: five pooling windows per thread
+// -> dy1 in shared memory (their loads are issued before the wait for the BN sums).  Phase B: thread = (channel, kh, 4 of the 28 rows)
 // with a 5-wide kw register tile.
 struct Conv1WgradArgs {
   BnBwdArgs bn;    // y = y1, dpool = d(pool1 out), layer = 0
@@ -459,19 +477,16 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
     c_mu = a.bn.st->mean[c]; c_is = a.bn.st->invstd[c];
     c_g = a.bn.params[OFF_G1 + c]; c_b = a.bn.params[OFF_BE1 + c];
   }
-  bn_backward_sums<16>(a.bn, s_k1, s_k2);
-  if (tid < 4) {
-    s_cst[tid][0] = c_mu; s_cst[tid][1] = c_is; s_cst[tid][2] = c_g; s_cst[tid][3] = c_b;
-    s_cst[tid][4] = s_k1[cg * 4 + tid]; s_cst[tid][5] = s_k2[cg * 4 + tid];
-  }
   for (int i = tid; i < 32 * C1_XS; i += C1W_THREADS) xs[i] = 0.f;
+  if (tid < 4) { s_cst[tid][0] = c_mu; s_cst[tid][1] = c_is; s_cst[tid][2] = c_g; s_cst[tid][3] = c_b; }
   const T* __restrict__ y1 = reinterpret_cast<const T*>(a.bn.y);
   const T* __restrict__ dp1 = reinterpret_cast<const T*>(a.bn.dpool);
   const int rs = tid % 7, kh = (tid / 7) % 5, col = tid / 35;  // valid for tid < 140
   float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f}, bsum = 0.f;
-
-  for (int n = blockIdx.x; n < a.bn.B; n += gridDim.x) {
-    __syncthreads();
+  // Phase A, part 1 for one image: the input tile into shared memory and this thread's five pooling windows
+  // (conv1 output + incoming gradient) into registers -- all loads issued together
+  float wv[5][4], wd[5];
+  auto fetch = [&](int n) {
     for (int i = tid; i < 196; i += C1W_THREADS) {
       const float4 v = load_pixels4(a.x, n, i);
       float* d = &xs[((4 * i) / 28 + 2) * C1_XS + (4 * i) % 28 + 2];
@@ -479,30 +494,47 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
     }
 #pragma unroll
     for (int it = 0; it < 5; ++it) {
+      const int e = min(tid + it * C1W_THREADS, 783);
+      const int cl = e / 196, w = e % 196, ph = w / 14, pw = w % 14, c = cg * 4 + cl;
+      const size_t off = (((size_t)n * 16 + c) * 28 + 2 * ph) * 28 + 2 * pw;
+      load2<T>(y1 + off, wv[it][0], wv[it][1]);
+      load2<T>(y1 + off + 28, wv[it][2], wv[it][3]);
+      wd[it] = ldf<T>(&dp1[((size_t)n * 16 + c) * 196 + w]);
+    }
+  };
+  // None of this depends on the predecessor (BN1 backward pass 1), only on kernels before it, which are complete
+  // once this grid runs: the first image is fetched BEFORE waiting for the sums
+  __syncthreads();
+  if ((int)blockIdx.x < a.bn.B) fetch(blockIdx.x);
+  bn_backward_sums<16>(a.bn, s_k1, s_k2);
+  if (threadIdx.x == 0) TRACE(12 * 16 + 1);
+  if (tid < 4) { s_cst[tid][4] = s_k1[cg * 4 + tid]; s_cst[tid][5] = s_k2[cg * 4 + tid]; }
+
+  for (int n = blockIdx.x; n < a.bn.B; n += gridDim.x) {
+    __syncthreads();
+    if (n != (int)blockIdx.x) fetch(n);
+#pragma unroll
+    for (int it = 0; it < 5; ++it) {
       const int e = tid + it * C1W_THREADS;
       if (e < 784) {
-        const int cl = e / 196, w = e % 196, ph = w / 14, pw = w % 14, c = cg * 4 + cl;
-        const size_t off = (((size_t)n * 16 + c) * 28 + 2 * ph) * 28 + 2 * pw;
-        float v[4];
-        load2<T>(y1 + off, v[0], v[1]);
-        load2<T>(y1 + off + 28, v[2], v[3]);
-        const float dd = ldf<T>(&dp1[((size_t)n * 16 + c) * 196 + w]);
+        const int cl = e / 196, w = e % 196, ph = w / 14, pw = w % 14;
         const float mu = s_cst[cl][0], is = s_cst[cl][1], g = s_cst[cl][2];
         bool live;
-        const int arg = pool_winner<T>(v, mu, is, g, s_cst[cl][3], live);
-        const float d = live ? dd : 0.f;
+        const int arg = pool_winner<T>(wv[it], mu, is, g, s_cst[cl][3], live);
+        const float d = live ? wd[it] : 0.f;
         const float k1 = s_cst[cl][4], k2 = s_cst[cl][5], k3 = is * g;
         float* dst = dy_s + (cl * 28 + 2 * ph) * 28 + 2 * pw;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const float da = (live && i == arg) ? d : 0.f;
-          dst[(i >> 1) * 28 + (i & 1)] = rnd<T>((da - k1 - (v[i] - mu) * k2) * k3);
+          dst[(i >> 1) * 28 + (i & 1)] = rnd<T>((da - k1 - (wv[it][i] - mu) * k2) * k3);
         }
       }
     }
     __syncthreads();
+    if (threadIdx.x == 0) TRACE(12 * 16 + 2);
     if (tid < 140) {
-#pragma unroll
+#pragma unroll 1  // rolled: less straight-line code to pull through a cold instruction cache
       for (int hh = 0; hh < 4; ++hh) {
         const int h = hh * 7 + rs;  // lanes of a warp read consecutive rows: bank-conflict free 16-byte loads
         const float* drow = dy_s + (col * 28 + h) * 28;
@@ -525,6 +557,7 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
       }
     }
   }
+  if (threadIdx.x == 0) TRACE(12 * 16 + 3);
   // fixed-order reduction over the 7 row groups
   if (tid < 140) {
 #pragma unroll
@@ -546,6 +579,7 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
     for (int r = 0; r < 7; ++r) v += red[(cl * 5 + 0) * 7 + r][5];
     row[OFF_B1 + cg * 4 + cl] = v;
   }
+  if (threadIdx.x == 0) TRACE(12 * 16 + 15);
 }
 
 }  // namespace dstep

@@ -187,6 +187,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_conv2_tc(Conv2TcArgs a) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_sync();  // predecessor wrote the input planes; barriers, TMEM and the filter tiles did not need it
+  if (threadIdx.x == 0) TRACE((MODE == 0 ? 3 : 10) * 16 + 1);
   const int n_img = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // images of this CTA
   // gridDim.y == 2 (small batches): each CTA computes ONE of the two M-tiles of its images, so twice as many SMs
   // share the MMA and epilogue work; gridDim.y == 1: both tiles, every image is fetched once
@@ -302,6 +303,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_conv2_tc(Conv2TcArgs a) {
   if (warp == 0) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+    if (threadIdx.x == 0) TRACE((MODE == 0 ? 3 : 10) * 16 + 15);
   }
   if (MODE == 0 && a.part != nullptr) {
     if (!a.defer && last_cta_done(&a.ds->ticket[1], gridDim.x * gridDim.y))

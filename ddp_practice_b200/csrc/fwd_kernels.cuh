@@ -51,6 +51,24 @@ template <> __device__ __forceinline__ void store2<__nv_bfloat16>(__nv_bfloat16*
   *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b);
 }
 
+// conv2's filter as ready-made tcgen05 B-operand tiles (conv2_tc.cuh): element i of [2][25][1 KB], gathered from the
+// fp32 master weights.  i < 12800: forward [tap][ci/8][co][ci%8]; else data gradient [tap'][co/8][ci][co%8], tap' = 24 - tap.
+template <typename T>
+__device__ __forceinline__ void w2_tile_gather(const float* __restrict__ params, void* tiles, int i) {
+  if (i >= 25600) return;
+  const int k8 = i & 7;
+  float w;
+  if (i < 12800) {
+    const int co = (i >> 3) & 31, kc = (i >> 8) & 1, tap = i >> 9;
+    w = params[OFF_W2 + (co * 16 + kc * 8 + k8) * 25 + tap];
+  } else {
+    const int j = i - 12800;
+    const int ci = (j >> 3) & 15, kc = (j >> 7) & 3, tp = j >> 9;
+    w = params[OFF_W2 + ((kc * 8 + k8) * 16 + ci) * 25 + (24 - tp)];
+  }
+  reinterpret_cast<T*>(tiles)[i] = Cvt<T>::from_f(w);
+}
+
 // ---------------------------------------------------------------------------------------
 // Local BN statistics from per-CTA (sum, sum of squares) partials; run by the last CTA of a
 // conv kernel.  `batch_norm_stats` (torch/nn/modules/_functions.py:39).  With SyncBN the
@@ -116,6 +134,10 @@ struct Conv1Args {
   CommDev comm;
   int B, dbl, sync;
   float eps;
+  // small-batch graph: CTAs with blockIdx.x >= conv_ctas rebuild the conv2 filter tiles (conv2_tc.cuh) instead of
+  // convolving, so the tiles are ready when this kernel completes and conv2 needs no extra graph branch / join
+  void* w2_tiles;
+  int conv_ctas;
 };
 
 constexpr int C1_XS = 36;       // padded row stride of the staged image
@@ -132,6 +154,10 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
   const int tid = threadIdx.x, cg = blockIdx.y;
   T* __restrict__ y1 = reinterpret_cast<T*>(a.y1);
   pdl_sync();  // first kernel of the step: nothing to wait for, lets the BN kernel start its prologue
+  if (a.w2_tiles != nullptr && (int)blockIdx.x >= a.conv_ctas) {
+    w2_tile_gather<T>(a.params, a.w2_tiles, (((int)blockIdx.x - a.conv_ctas) * C1_GROUPS + cg) * C1_THREADS + tid);
+    return;
+  }
 
   for (int i = tid; i < 32 * C1_XS; i += C1_THREADS) xs[i] = 0.f;
   if (tid < 100) {  // ws[k][j] <- rnd(W1[cg*4+j][k])
@@ -155,15 +181,8 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
       d[0] = rnd<T>(v.x); d[1] = rnd<T>(v.y); d[2] = rnd<T>(v.z); d[3] = rnd<T>(v.w);
     }
     __syncthreads();
+    if (threadIdx.x == 0) TRACE(1 * 16 + 1);
     if (!active) continue;
-    float in[6][8];
-#pragma unroll
-    for (int r = 0; r < 6; ++r) {
-      const float4 u = *reinterpret_cast<const float4*>(&xs[(2 * tr + r) * C1_XS + 4 * tc]);
-      const float4 v = *reinterpret_cast<const float4*>(&xs[(2 * tr + r) * C1_XS + 4 * tc + 4]);
-      in[r][0] = u.x; in[r][1] = u.y; in[r][2] = u.z; in[r][3] = u.w;
-      in[r][4] = v.x; in[r][5] = v.y; in[r][6] = v.z; in[r][7] = v.w;
-    }
     float acc[2][4][4];
 #pragma unroll
     for (int r = 0; r < 2; ++r)
@@ -171,8 +190,19 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
       for (int c = 0; c < 4; ++c)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[r][c][j] = 0.f;
+    // the kh loop stays rolled on purpose: the step runs ~14 different kernels back to back, more code than the
+    // SM's instruction cache holds, so straight-line code is fetched from L2 on every launch (measured: the fully
+    // unrolled 800-FMA body ran at ~2.7 cycles per instruction)
+#pragma unroll 1
+    for (int kh = 0; kh < 5; ++kh) {
+      float in[2][8];
 #pragma unroll
-    for (int kh = 0; kh < 5; ++kh)
+      for (int r = 0; r < 2; ++r) {
+        const float4 u = *reinterpret_cast<const float4*>(&xs[(2 * tr + r + kh) * C1_XS + 4 * tc]);
+        const float4 v = *reinterpret_cast<const float4*>(&xs[(2 * tr + r + kh) * C1_XS + 4 * tc + 4]);
+        in[r][0] = u.x; in[r][1] = u.y; in[r][2] = u.z; in[r][3] = u.w;
+        in[r][4] = v.x; in[r][5] = v.y; in[r][6] = v.z; in[r][7] = v.w;
+      }
 #pragma unroll
       for (int kw = 0; kw < 5; ++kw) {
         const float4 w0 = *reinterpret_cast<const float4*>(&ws[(kh * 5 + kw) * 4]);
@@ -181,11 +211,12 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
         for (int r = 0; r < 2; ++r)
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
-            const float v = in[r + kh][c + kw];
+            const float v = in[r][c + kw];
 #pragma unroll
             for (int j = 0; j < 4; ++j) acc[r][c][j] = fmaf(v, w[j], acc[r][c][j]);
           }
       }
+    }
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int ch = cg * 4 + j;
@@ -204,6 +235,7 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
     }
   }
   if (a.part == nullptr) return;  // eval: running statistics are used, none are gathered
+  if (threadIdx.x == 0) TRACE(1 * 16 + 2);
   __syncthreads();
   const int warp = tid >> 5, lane = tid & 31;
 #pragma unroll
@@ -217,6 +249,7 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
     const float v = ((red[0][tid] + red[1][tid]) + red[2][tid]) + red[3][tid];
     a.part[((size_t)blockIdx.x * 16 + cg * 4 + j) * 2 + stat] = v;
   }
+  if (threadIdx.x == 0) TRACE(1 * 16 + 15);
   if (a.defer) return;
   if (last_cta_done(&a.ds->ticket[0], gridDim.x * gridDim.y))
     finalize_fwd_stats<16>(a.part, gridDim.x, (float)a.B * 784.f, a.eps, a.st, 0, a.comm, a.ds, a.sync);
@@ -260,9 +293,19 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
     const int lanes = min((int)blockDim.x / COLS, 512 / COLS);
     const int col = c % COLS, lane = c / COLS;
     if (lane < lanes) {
+      // deferred mode means at most 64 rows: every load of this thread is issued before the first one is
+      // consumed (ONE trip to L2 instead of rows / lanes / 4 of them); the sum keeps its row order
+      constexpr int NV = 64 / (256 / COLS);
+      float v[NV];
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int r = lane + i * lanes;
+        v[i] = r < a.rows ? __ldcg(&a.part[(size_t)r * COLS + col]) : 0.f;
+      }
       double acc = 0.0;
-#pragma unroll 4
-      for (int r = lane; r < a.rows; r += lanes) acc += (double)__ldcg(&a.part[(size_t)r * COLS + col]);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) acc += (double)v[i];
+      for (int r = lane + NV * lanes; r < a.rows; r += lanes) acc += (double)__ldcg(&a.part[(size_t)r * COLS + col]);
       fin[lane * COLS + col] = acc;
     }
     __syncthreads();
@@ -353,12 +396,23 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
     s_b[threadIdx.x] = a.params[OFF_BE + threadIdx.x];
   }
   pdl_sync();  // predecessor: the conv kernel that produced y and the partial statistics
-  bn_forward_stats<C>(a, s_mean, s_invstd, RM, RV, (float)a.B * (float)(H * H));
-  if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 1);
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   T* __restrict__ p = reinterpret_cast<T*>(a.p);
   const size_t total = (size_t)a.B * C * HP * HP;
   const size_t stride = (size_t)gridDim.x * 256;
+  size_t idx0 = (size_t)blockIdx.x * 256 + threadIdx.x;
+  // small batch (fewer than four windows per thread): the first window is fetched before the statistics are
+  // reduced, so its trip to L2 overlaps the reduction's
+  const bool pre = idx0 < total && idx0 + 3 * stride >= total;
+  float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
+  if (pre) {
+    const int pw = (int)(idx0 % HP), ph = (int)((idx0 / HP) % HP);
+    const T* src = y + ((idx0 / (HP * HP)) * H + 2 * ph) * H + 2 * pw;
+    load2<T>(src, q0, q1);
+    load2<T>(src + H, q2, q3);
+  }
+  bn_forward_stats<C>(a, s_mean, s_invstd, RM, RV, (float)a.B * (float)(H * H));
+  if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 1);
   auto emit = [&](size_t idx, float v0, float v1, float v2, float v3) {
     const int pw = (int)(idx % HP), ph = (int)((idx / HP) % HP);
     const size_t plane = idx / (HP * HP);
@@ -375,7 +429,7 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
       stf<T>(reinterpret_cast<T*>(a.p_planes) + (((size_t)(n * 2 + (c >> 3)) * 320 + (ph + 3) * 16 + pw) * 8 + (c & 7)), m);
     }
   };
-  size_t idx0 = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (pre) { emit(idx0, q0, q1, q2, q3); idx0 += stride; }
   for (; idx0 + 3 * stride < total; idx0 += 4 * stride) {  // large batch: four outputs per iteration, loads first
     float vv[4][4];
 #pragma unroll
@@ -591,6 +645,7 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
 #pragma unroll
   for (int j = 0; j < 10; ++j) b[j] = rnd<T>(a.params[OFF_BFC + j]);
   pdl_sync();  // predecessor: BN2 + ReLU + pool (p2); the weights above do not depend on it
+  if (threadIdx.x == 0) TRACE(5 * 16 + 1);
   // incoming gradient of the loss: `scale` cast to the loss dtype (65536 -> inf in fp16)
   const float gl = a.use_scaler ? rnd<T>(a.ds->scale) : 1.0f;
   const float g = rnd<T>(-(gl / (float)a.B));
@@ -672,6 +727,7 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
     }
     __syncthreads();
   }
+  if (threadIdx.x == 0) TRACE(5 * 16 + 15);
 }
 
 }  // namespace dstep

@@ -16,7 +16,7 @@
 #pragma once
 #include <cooperative_groups.h>
 
-#include "common.cuh"
+#include "fwd_kernels.cuh"
 
 namespace dstep {
 namespace cg = cooperative_groups;
@@ -44,10 +44,10 @@ struct StepArgs {
 
 // conv2's filter is kept, besides its fp32 master copy, as ready-made tcgen05 B operands
 // (conv2_tc.cuh): 25 taps x [K chunk][N row][8] in the autocast dtype, once for the forward
-// (N = co, K = ci) and once for the data gradient (N = ci, K = co, taps flipped).  A small
-// kernel on a side branch at the head of every step graph rebuilds them from the fp32 weights
-// (parallel to conv1, off the critical path), so the conv kernels fetch their 25 KB with a
-// single TMA copy.  (The reference re-casts every weight on every forward: autocast_mode.h:824.)
+// (N = co, K = ci) and once for the data gradient (N = ci, K = co, taps flipped).  They are
+// rebuilt from the fp32 weights at the head of every step -- by 200 extra CTAs of the conv1
+// kernel at small batch, by k_refresh_w2_tiles on a side branch of the graph when conv1 runs on
+// the tensor cores -- so the conv kernels fetch their 25 KB with a single TMA copy.  (The reference re-casts every weight on every forward: autocast_mode.h:824.)
 // Doing this from inside the SGD kernel was measured at +7 us: 25,600 scattered 2-byte stores
 // issued by 4 SMs.
 // Sum the conv2 weight-gradient partial rows (one per wgrad CTA) in fixed row order, spread
@@ -68,20 +68,7 @@ __global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ g
 
 template <typename T>
 __global__ void __launch_bounds__(256) k_refresh_w2_tiles(const float* __restrict__ params, void* tiles) {
-  // one thread per tile element (gather from the 51 KB filter, coalesced 2-byte stores)
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= 25600) return;
-  const int k8 = i & 7;
-  float w;
-  if (i < 12800) {  // forward: [tap][ci/8][co][ci%8]
-    const int co = (i >> 3) & 31, kc = (i >> 8) & 1, tap = i >> 9;
-    w = params[OFF_W2 + (co * 16 + kc * 8 + k8) * 25 + tap];
-  } else {          // data gradient: [tap'][co/8][ci][co%8], tap' = 24 - tap
-    const int j = i - 12800;
-    const int ci = (j >> 3) & 15, kc = (j >> 7) & 3, tp = j >> 9;
-    w = params[OFF_W2 + ((kc * 8 + k8) * 16 + ci) * 25 + (24 - tp)];
-  }
-  reinterpret_cast<T*>(tiles)[i] = Cvt<T>::from_f(w);
+  w2_tile_gather<T>(params, tiles, blockIdx.x * 256 + threadIdx.x);  // one thread per tile element, coalesced stores
 }
 
 template <typename T>
@@ -104,11 +91,19 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     else { p4.x = a.params[e]; p4.y = a.params[e + 1]; }
   }
   pdl_sync();  // predecessor: conv1 weight gradient (the side branches are joined by full dependencies)
+  if (threadIdx.x == 0) TRACE(13 * 16 + 1);
   // CTA 0 owns the conv1 region (elements 0..415), whose gradient arrives as one partial row per
   // conv1-wgrad CTA: all 1024 threads sum it together (9 row lanes per float4, one round trip to
   // L2 instead of rows/8), fixed order.  Warp 0 also fetches the per-image losses now.
   __shared__ float4 s_c1[9][104];
   float nll_pref = 0.f;
+  // CTA 0's other elements (BN affine gradients, the head of conv2's filter) need one row each: that load is issued
+  // before the cooperative sum so both travel to L2 together
+  float4 pre = make_float4(0.f, 0.f, 0.f, 0.f);
+  const bool pre_direct = cta == 0 && e >= OFF_G1 && e < OFF_W2;
+  const bool pre_red = cta == 0 && e >= OFF_W2 && a.gred != nullptr;  // CTA 0 ends at element 4095 < OFF_B2
+  if (pre_direct) pre = __ldcg(reinterpret_cast<const float4*>(a.gdirect + e));
+  if (pre_red) pre = __ldcg(reinterpret_cast<const float4*>(a.gred + e));
   if (cta == 0) {
     const int e4 = tid % 104, rl = tid / 104;
     if (rl < 9) {
@@ -135,7 +130,11 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     else if (e < OFF_G2) rows = a.rows_conv2b;
     else if (e < OFF_WFC) { rows = 0; round_t = false; }
     else rows = a.rows_fc;
-    if (round_t) {
+    if (pre_direct) {
+      g = pre;
+    } else if (pre_red) {
+      g = make_float4(rnd<T>(pre.x), rnd<T>(pre.y), rnd<T>(pre.z), rnd<T>(pre.w));
+    } else if (round_t) {
       const float* p = a.gpart + e;
       if (a.gred != nullptr && e >= OFF_W2 && e < OFF_B2) { p = a.gred + e; rows = 1; }
       if (e < OFF_G1) {  // conv1 region: lanes summed above, combine in fixed order
@@ -158,6 +157,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     if (e + 4 > N_PARAM) { g.z = 0.f; g.w = 0.f; }
   }
 
+  if (threadIdx.x == 0) TRACE(13 * 16 + 2);
   // ---- 2. DDP all-reduce: pre-divide, push to every peer's inbox, flag, wait, sum in rank order
   const float inv_w = 1.0f / (float)W;
   float4 h = make_float4(g.x * inv_w, g.y * inv_w, g.z * inv_w, g.w * inv_w);
@@ -207,6 +207,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     }
   }
 
+  if (threadIdx.x == 0) TRACE(13 * 16 + 3);
   // ---- 3. unscale + non-finite check (every element is multiplied, finite or not)
   float4 u = tot;
   if (a.use_scaler) {
@@ -221,12 +222,14 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   __syncthreads();
   if (tid < STEP_CTAS) *cluster.map_shared_rank(&s_flags[cta], tid) = s_nonfinite;
   cluster.sync();
+  if (threadIdx.x == 0) TRACE(13 * 16 + 4);
   int found = 0;
 #pragma unroll
   for (int r = 0; r < STEP_CTAS; ++r) found |= s_flags[r];
 
   // the gradient taps are stored only now: a release at cluster scope waits for every global
   // store issued before it, so none may be in flight while the barrier above runs
+  if (threadIdx.x == 0) TRACE(13 * 16 + 5);
   if (valid) {
     if (e + 4 <= N_PARAM) {
       *reinterpret_cast<float4*>(a.grads_scaled + e) = tot;
@@ -250,6 +253,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     }
   }
 
+  if (threadIdx.x == 0) TRACE(13 * 16 + 6);
   // ---- 6. scalar state: loss, scale, tracker, epoch
   if (cta == 0 && tid < 32) {
     float s = warp_sum(nll_pref);
