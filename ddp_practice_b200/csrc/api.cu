@@ -55,7 +55,13 @@ struct ddpstep_ctx {
   void *dflat = nullptr, *dy2 = nullptr, *dp1 = nullptr;
   void *p1h = nullptr, *dy2h = nullptr, *w2_tiles = nullptr;  // padded-plane copies for the tcgen05 conv2 path (zero halos, written once at alloc)
   bool use_tc = false, use_wgrad_tc = false, use_pdl = true, last_planes = false, use_conv1_tc = true, use_conv1_wgrad_tc = true;
+  // small grids (<= 64 partial rows): 2 = tagged rows, the BN consumer's first CTA publishes the statistics before its grid
+  // dependency resolves; 1 = plain rows, every consumer CTA reduces them; 0 = the producer's last CTA finalises (DDPSTEP_DEFER)
+  int defer_stats = 2;
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
+  // the same partial rows as tagged 8-byte words (store_partial), one buffer per producer so that a tag can never match
+  // another stage's words of the same step
+  float *part1_ll = nullptr, *part2_ll = nullptr, *bpart1_ll = nullptr, *bpart2_ll = nullptr;
   float* x_stage = nullptr;
   int64_t* y_stage = nullptr;
   // comm
@@ -139,6 +145,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   A(logits, B * 10 * es); A(dlogits, B * 10 * es); A(dflat, B * 1568 * es); A(dy2, B * 32 * 196 * es);
   A(dp1, B * 16 * 196 * es); A(nll, B * 4);
   A(part1, 296 * 16 * 2 * 4); A(part2, 296 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
+  A(part1_ll, 64 * 32 * 8); A(part2_ll, 64 * 64 * 8); A(bpart1_ll, 16 * 64 * 2 * 8); A(bpart2_ll, 32 * 64 * 2 * 8);
   A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
   A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4);
   {
@@ -150,6 +157,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
     ctx->use_conv1_tc = !(envc && envc[0] == '0');
     const char* envp = getenv("DDPSTEP_PDL");
     ctx->use_pdl = !(envp && envp[0] == '0');
+    const char* envd = getenv("DDPSTEP_DEFER");
+    if (envd && envd[0] >= '0' && envd[0] <= '2') ctx->defer_stats = envd[0] - '0';
     const char* envw = getenv("DDPSTEP_WGRAD_TC");
     ctx->use_wgrad_tc = ctx->use_tc && !(envw && envw[0] == '0');
   }
@@ -219,7 +228,8 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
   void* bufs[] = {ctx->params, ctx->grads, ctx->grads_scaled, ctx->bnbuf, ctx->nbt, ctx->ds, ctx->st, ctx->counts,
                   ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->logits, ctx->dlogits, ctx->dflat, ctx->dy2, ctx->dp1,
                   ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
-                  ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h, ctx->w2_tiles, ctx->gred};
+                  ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h, ctx->w2_tiles, ctx->gred,
+                  ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll};
   for (void* p : bufs) if (p) cudaFree(p);
   if (ctx->host_mail) cudaFreeHost(const_cast<float*>(ctx->host_mail));
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
@@ -389,8 +399,8 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   const int g1 = std::min(B, 296);
   // small grids: the BN kernels reduce the conv kernels' partial sums themselves (no last-CTA tail)
   const int tsplit = B <= 64 ? 2 : 1;  // tcgen05 conv2: one M-tile per CTA at small batch
-  const int defer1 = g1 <= 64, defer2 = std::min(B, 296) <= 64;
-  Conv1Args a1{x, c->params, c->y1, c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps,
+  const int defer1 = g1 <= 64 ? c->defer_stats : 0, defer2 = std::min(B, 296) <= 64 ? c->defer_stats : 0;
+  Conv1Args a1{x, c->params, c->y1, defer1 == 2 ? c->part1_ll : c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps,
                tiles_in_conv1 ? c->w2_tiles : nullptr, g1};
   constexpr int kTileCtas = 25600 / (C1_GROUPS * C1_THREADS);  // 50 extra blockIdx.x values x 4 groups x 128 threads
   if (rec) rec->a_c1 = a1;
@@ -409,7 +419,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   mark();
   // 2. BN1 + ReLU + pool
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps,
-                defer1 ? c->part1 : nullptr, rows1};
+                defer1 == 2 ? c->part1_ll : defer1 ? c->part1 : nullptr, rows1, defer1 == 2};
   bool planes = false;
   // large batches: write p1 / d(conv2 out) only as padded planes with 16-byte stores (nobody reads the NCHW copies);
   // small batches keep the one-thread-per-element kernels, whose shorter per-thread chains give lower latency
@@ -424,13 +434,13 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   mark();
   // 3. conv2 + local BN2 statistics
   const int g2 = std::min(B, 296);  // tensor-core path: up to two CTAs per SM
-  Conv14Args a2{c->p1, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+  Conv14Args a2{c->p1, c->params, c->y2, defer2 == 2 ? c->part2_ll : c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
   bool tc = false;
   if constexpr (!std::is_same<T, float>::value) {
     if (c->use_tc) {  // tcgen05 implicit GEMM on the padded planes written by kernel 2
       tc = true;
       if (fork && !tiles_in_conv1) cudaStreamWaitEvent(s, c->ev_j0, 0);
-      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
+      Conv2TcArgs t2{c->w2_tiles, c->p1h, c->params, c->y2, defer2 == 2 ? c->part2_ll : c->part2, defer2, st2, c->ds, c->comm, B, dbl, sync, cfg.bn_eps};
       launch_k(k_conv2_tc<T, 0>, dim3(g2, tsplit), dim3(TC_THREADS), tc_smem_bytes(2), s, t2, pdl);
     }
   }
@@ -438,7 +448,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   mark();
   // 4. BN2 + ReLU + pool
   BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps,
-                defer2 ? c->part2 : nullptr, tc ? g2 * tsplit : g2};
+                defer2 == 2 ? c->part2_ll : defer2 ? c->part2 : nullptr, tc ? g2 * tsplit : g2, defer2 == 2};
   launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark();
   // 5. Linear + CE + dlogits + d(pool2 out)
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, c->dlogits, c->dflat, c->nll, c->counts,
@@ -455,7 +465,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   if (fork) cudaEventRecord(c->ev_j1, s1);
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);
-  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, 1, ns2, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
+  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->defer_stats == 2 ? c->bpart2_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->defer_stats, ns2, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
   // the plane-writing apply kernel has 4 channel groups per batch split: use more splits to fill the GPU
   const int ns2p = clampi(cdiv(B, 2), 1, 64);
   BnBwdArgs r2p = r2;
@@ -501,7 +511,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   if (fork) cudaEventRecord(c->ev_j2, s2);
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
   const int ns1 = clampi(cdiv(B, 2), 1, 32);
-  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, 1, ns1, nullptr, nullptr, c->gpart};
+  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->defer_stats == 2 ? c->bpart1_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, c->defer_stats, ns1, nullptr, nullptr, c->gpart};
   launch_k(k_bn_bwd_reduce<T, 16, 28>, dim3(16, ns1), dim3(256), 0, s, r1, pdl); mark();
   const int gc1 = std::min(B, 296);
   Conv1WgradArgs cw{r1, x};

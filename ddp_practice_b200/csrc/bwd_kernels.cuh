@@ -82,6 +82,8 @@ struct BnBwdArgs {
   CommDev comm;
   int B, per_split, layer, sync;
   int defer, nsplit;  // defer = 1: pass 1 only writes bpart; the consumer of the sums reduces the nsplit rows
+                      // defer = 2: same, bpart holds tagged words and the consumer's first CTA publishes the sums
+                      // before it waits for the grid dependency (as bn_forward_publish does)
   // pass 2 only
   void* dy;           // [B,C,H,H] gradient at the conv output
   void* dy_planes;    // optional second copy in the padded-plane layout (conv2_tc.cuh), layer 2 only
@@ -99,6 +101,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
   const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G + c], b = a.params[OFF_BE + c];
+  const unsigned int ll_tag = (unsigned int)a.ds->epoch + 1u;
   pdl_sync();  // predecessor produced dpool; the statistics above come from an earlier kernel
   if (threadIdx.x == 0) TRACE((C == 32 ? 7 : 11) * 16 + 1);
   float sdy = 0.f, sdyx = 0.f;
@@ -148,7 +151,7 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
   if (tid < 2) {
     float v = 0.f;
     for (int w = 0; w < 8; ++w) v += red[w][tid];
-    a.bpart[((size_t)c * gridDim.y + blockIdx.y) * 2 + tid] = v;
+    store_partial(a.bpart, ((size_t)c * gridDim.y + blockIdx.y) * 2 + tid, v, a.defer == 2, ll_tag);
   }
   if (threadIdx.x == 0) TRACE((C == 32 ? 7 : 11) * 16 + 15);
   if (a.defer) return;
@@ -190,42 +193,78 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
   // issued first so that their latency hides behind the partial-sum loads below
   float n_tot = 0.f, inv_c = 0.f;
   if (c < C) { n_tot = a.st->n_total; inv_c = a.st->invstd[c]; }
-  pdl_sync();  // predecessor: pass 1 (bpart)
-  if (a.defer) {
-    // this rank's sums from the pass-1 partials: thread = (quarter of the rows, channel, which sum), so the
-    // loads overlap; quarters are combined in fixed order.  CTA (0,0) also publishes d(gamma), d(beta) and,
-    // under SyncBN, pushes the sums to every rank
-    __shared__ float s_q[4][2 * C];
+  const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
+  // this rank's sums from the pass-1 partials: thread = (quarter of the rows, channel, which sum), so the
+  // loads overlap; quarters are combined in fixed order.  CTA (0,0) also publishes d(gamma), d(beta) and
+  // pushes the sums to the ranks that need them
+  __shared__ float s_q[4][2 * C];
+  auto local_sums = [&](bool ll) {
     if (c < 8 * C) {
       const int qd = c / (2 * C), ch = (c % (2 * C)) >> 1, which = c & 1;
       double acc = 0.0;
+      if (ll) {  // tagged rows (at most 64, i.e. 16 per thread): polled until they carry this step's tag
+        const llword* rows = reinterpret_cast<const llword*>(a.bpart);
+        float v[16];
+        long long t0 = 0;
+        for (int spin = 0;; ++spin) {
+          llword w[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int sp = qd + 4 * i;
+            w[i] = sp < a.nsplit ? ll_ld(&rows[((size_t)ch * a.nsplit + sp) * 2 + which]) : ((llword)tag << 32);
+          }
+          bool ok = true;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ok = ok && ((unsigned int)(w[i] >> 32) == tag);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = __uint_as_float((unsigned int)w[i]);
+          if (ok) break;
+          if (spin == 64) t0 = clock64();
+          if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(&a.ds->error, 1); break; }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc += (double)v[i];  // rows past nsplit contribute +0.0
+      } else {
 #pragma unroll 8
-      for (int sp = qd; sp < a.nsplit; sp += 4) acc += (double)__ldcg(&a.bpart[((size_t)ch * a.nsplit + sp) * 2 + which]);
+        for (int sp = qd; sp < a.nsplit; sp += 4) acc += (double)__ldcg(&a.bpart[((size_t)ch * a.nsplit + sp) * 2 + which]);
+      }
       s_q[qd][which * C + ch] = (float)acc;
     }
     __syncthreads();
     if (c < 2 * C) s_loc[c] = ((s_q[0][c] + s_q[1][c]) + s_q[2][c]) + s_q[3][c];
     __syncthreads();
-    if (first) {
-      if (c < C) {
-        a.gdirect[OFF_G + c] = s_loc[C + c] * inv_c;  // d(gamma), local: DDP averages it
-        a.gdirect[OFF_BE + c] = s_loc[c];                        // d(beta)
-        if (xchg) {  // the all_reduce of _functions.py:159 as pushed self-validating words
-          const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
-          for (int q = 0; q < a.comm.world; ++q) {
-            llword* slot = a.comm.peer[q]->ll_bn_bwd[a.layer][a.comm.rank];
-            ll_store(&slot[c], s_loc[c], tag);
-            ll_store(&slot[C + c], s_loc[C + c], tag);
-          }
-        }
+  };
+  auto publish = [&](bool self_too) {
+    if (c < C) {
+      a.gdirect[OFF_G + c] = s_loc[C + c] * inv_c;  // d(gamma), local: DDP averages it
+      a.gdirect[OFF_BE + c] = s_loc[c];             // d(beta)
+      for (int q = 0; q < a.comm.world; ++q) {  // the all_reduce of _functions.py:159 as pushed tagged words
+        if (q == a.comm.rank ? !self_too : !xchg) continue;
+        llword* slot = a.comm.peer[q]->ll_bn_bwd[a.layer][a.comm.rank];
+        ll_store(&slot[c], s_loc[c], tag);
+        ll_store(&slot[C + c], s_loc[C + c], tag);
       }
     }
+  };
+  const bool polled = a.defer == 2;
+  if (polled && first) {  // before the wait: the rows are picked up while the pass-1 grid is still draining
+    local_sums(true);
+    publish(true);
+  }
+  pdl_sync();  // predecessor: pass 1 (bpart)
+  if (a.defer == 1) {
+    local_sums(false);
+    if (first) publish(xchg);
   }
   if (c < C) {
     float s0, s1;
-    if (xchg) {
+    if (polled && !xchg) {  // single rank: the words CTA (0,0) published
+      float got[2];
+      const int idx[2] = {c, C + c};
+      ll_gather<2, 1>(&a.comm.self->ll_bn_bwd[a.layer][a.comm.rank][0], 64, idx, 0, 1, tag, got, &a.ds->error);
+      s0 = got[0]; s1 = got[1];
+    } else if (xchg) {
       s0 = 0.f; s1 = 0.f;
-      const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
       float got[MAX_WORLD * 2];
       const int idx[2] = {c, C + c};
       ll_gather<2>(&a.comm.self->ll_bn_bwd[a.layer][0][0], 64, idx, 0, a.comm.world, tag, got, &a.ds->error);

@@ -70,8 +70,9 @@ __device__ __forceinline__ float4 load_pixels4(const BatchSrc& b, int n, int i) 
 // __threadfence_system, no separate flag store, no ordering between words: one NVLink store latency
 // per exchange.  Tags are epoch + 1 (never 0, never reused), so stale words can never match.
 typedef unsigned long long llword;
+constexpr int BN_FWD_SLOT = 104;  // 3 x 32 channels + count, padded
 struct alignas(128) SymRegion {
-  alignas(128) llword ll_bn_fwd[2][MAX_WORLD][72];   // [layer][sender]: mean[C] invstd[C] count
+  alignas(128) llword ll_bn_fwd[2][MAX_WORLD][BN_FWD_SLOT];  // [layer][sender]: mean[C] invstd[C] unbiased var[C] count
   alignas(128) llword ll_bn_bwd[2][MAX_WORLD][64];   // [layer][sender]: sum_dy[C] sum_dy_xmu[C]
   alignas(128) llword ll_bnbuf[N_BNBUF + 4];         // rank 0's running buffers + 2 x nbt (lo, hi) (plain-BN DDP)
   alignas(128) llword ll_inbox[2][MAX_WORLD][N_PAD]; // [step parity][sender][bucket element]
@@ -126,6 +127,13 @@ __device__ __forceinline__ llword ll_pack(float v, unsigned int tag) {
 }
 __device__ __forceinline__ void ll_store(llword* p, float v, unsigned int tag) {
   asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(ll_pack(v, tag)) : "memory");
+}
+// Partial-sum rows between a producer kernel and the BN kernel after it come in two formats: plain fp32 (the
+// consumer reads them after the grid dependency resolved) or tagged words like the cross-GPU ones ("ll rows"), which
+// ONE CTA of the consumer can poll while the producer grid is still draining -- see bn_forward_publish.
+__device__ __forceinline__ void store_partial(float* part, size_t i, float v, int ll, unsigned int tag) {
+  if (ll) ll_store(reinterpret_cast<llword*>(part) + i, v, tag);
+  else part[i] = v;
 }
 // Poll a word of this rank's own region until its tag matches; ~4 s timeout raises the error word.
 __device__ __forceinline__ float ll_wait(const llword* p, unsigned int tag, int* err) {

@@ -186,6 +186,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_conv2_tc(Conv2TcArgs a) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const unsigned int ll_tag = (unsigned int)a.ds->epoch + 1u;  // for the partial-row stores at the very end
   pdl_sync();  // predecessor wrote the input planes; barriers, TMEM and the filter tiles did not need it
   if (threadIdx.x == 0) TRACE((MODE == 0 ? 3 : 10) * 16 + 1);
   const int n_img = (a.B - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // images of this CTA
@@ -297,7 +298,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_conv2_tc(Conv2TcArgs a) {
     if (tid < 64) {
       const float acc = ((red[tid] + red[64 + tid]) + red[128 + tid]) + red[192 + tid];
       const int c = tid & 31, stat = tid >> 5;
-      a.part[((size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 32 + c) * 2 + stat] = acc;
+      store_partial(a.part, ((size_t)(blockIdx.y * gridDim.x + blockIdx.x) * 32 + c) * 2 + stat, acc, a.defer == 2, ll_tag);
     }
   }
   if (warp == 0) {

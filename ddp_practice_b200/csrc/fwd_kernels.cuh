@@ -111,7 +111,7 @@ __device__ void finalize_fwd_stats(const float* part, int rows, float count, flo
         llword* slot = comm.peer[q]->ll_bn_fwd[layer][comm.rank];
         ll_store(&slot[c], (float)mean, tag);
         ll_store(&slot[C + c], invstd, tag);
-        if (c == 0) ll_store(&slot[2 * C], count, tag);
+        if (c == 0) ll_store(&slot[3 * C], count, tag);
       }
     }
   }
@@ -128,7 +128,8 @@ struct Conv1Args {
   const float* params;
   void* y1;
   float* part;  // [gridDim.x][16][2]
-  int defer;    // 1: leave the partial sums to the consumer (bn_forward_stats), no last-CTA finalisation
+  int defer;    // 1: leave the partial sums to the consumer (bn_forward_stats), no last-CTA finalisation;
+                // 2: same, and `part` holds tagged 8-byte words (store_partial)
   BnStat* st;
   DevState* ds;
   CommDev comm;
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
   __shared__ float red[4][8];
   const int tid = threadIdx.x, cg = blockIdx.y;
   T* __restrict__ y1 = reinterpret_cast<T*>(a.y1);
+  const unsigned int ll_tag = (unsigned int)a.ds->epoch + 1u;  // needed only at the very end: fetched now
   pdl_sync();  // first kernel of the step: nothing to wait for, lets the BN kernel start its prologue
   if (a.w2_tiles != nullptr && (int)blockIdx.x >= a.conv_ctas) {
     w2_tile_gather<T>(a.params, a.w2_tiles, (((int)blockIdx.x - a.conv_ctas) * C1_GROUPS + cg) * C1_THREADS + tid);
@@ -247,12 +249,12 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
   if (tid < 8) {  // tid = stat*4 + j
     const int stat = tid >> 2, j = tid & 3;
     const float v = ((red[0][tid] + red[1][tid]) + red[2][tid]) + red[3][tid];
-    a.part[((size_t)blockIdx.x * 16 + cg * 4 + j) * 2 + stat] = v;
+    store_partial(a.part, ((size_t)blockIdx.x * 16 + cg * 4 + j) * 2 + stat, v, a.defer == 2, ll_tag);
   }
   if (threadIdx.x == 0) TRACE(1 * 16 + 15);
   if (a.defer) return;
-  if (last_cta_done(&a.ds->ticket[0], gridDim.x * gridDim.y))
-    finalize_fwd_stats<16>(a.part, gridDim.x, (float)a.B * 784.f, a.eps, a.st, 0, a.comm, a.ds, a.sync);
+  if (last_cta_done(&a.ds->ticket[0], a.conv_ctas * gridDim.y))  // the filter-tile CTAs returned long ago
+    finalize_fwd_stats<16>(a.part, a.conv_ctas, (float)a.B * 784.f, a.eps, a.st, 0, a.comm, a.ds, a.sync);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -277,59 +279,121 @@ struct BnPoolArgs {
   // the producer.  part == nullptr: the producer finalised (large grids) and st->l* are valid.
   const float* part;
   int rows;
+  int ll;  // `part` holds tagged words: CTA 0 publishes the local statistics early (bn_forward_publish), the others poll
 };
+
+// Local statistics from the producer's partial rows (column = (channel, stat), several row lanes per column, sums in
+// double, divisions / square root in fp32 as batch_norm_stats does).  Called by every thread of a 256-thread CTA.
+// LL = true: the rows are tagged words that are polled until they carry this step's tag.
+template <int C, bool LL>
+__device__ void bn_local_stats(const BnPoolArgs& a, float local_count, unsigned int tag, float& lmean, float& linvstd,
+                               float& lvar_unb) {
+  __shared__ double fin[512];
+  constexpr int COLS = 2 * C;
+  const int c = threadIdx.x;
+  const int lanes = min((int)blockDim.x / COLS, 512 / COLS);
+  const int col = c % COLS, lane = c / COLS;
+  if (lane < lanes) {
+    // deferred mode means at most 64 rows: every load of this thread is issued before the first one is
+    // consumed (ONE trip to L2 instead of rows / lanes / 4 of them); the sum keeps its row order
+    constexpr int NV = 64 / (256 / COLS);
+    float v[NV];
+    if (LL) {
+      const llword* rows = reinterpret_cast<const llword*>(a.part);
+      long long t0 = 0;
+      for (int spin = 0;; ++spin) {
+        llword w[NV];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int r = lane + i * lanes;
+          w[i] = r < a.rows ? ll_ld(&rows[(size_t)r * COLS + col]) : ((llword)tag << 32);
+        }
+        bool ok = true;
+#pragma unroll
+        for (int i = 0; i < NV; ++i) ok = ok && ((unsigned int)(w[i] >> 32) == tag);
+#pragma unroll
+        for (int i = 0; i < NV; ++i) v[i] = __uint_as_float((unsigned int)w[i]);
+        if (ok) break;
+        if (spin == 64) t0 = clock64();
+        if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(&a.ds->error, 1); break; }
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int r = lane + i * lanes;
+        v[i] = r < a.rows ? __ldcg(&a.part[(size_t)r * COLS + col]) : 0.f;
+      }
+    }
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) acc += (double)v[i];
+    if (!LL)
+      for (int r = lane + NV * lanes; r < a.rows; r += lanes) acc += (double)__ldcg(&a.part[(size_t)r * COLS + col]);
+    fin[lane * COLS + col] = acc;
+  }
+  __syncthreads();
+  if (c < C) {
+    double sm = 0.0, sq = 0.0;
+    for (int l = 0; l < lanes; ++l) { sm += fin[l * COLS + 2 * c]; sq += fin[l * COLS + 2 * c + 1]; }
+    // sums are combined in double; the few divisions / the square root run in fp32 (an fp64 divide and
+    // sqrt chain costs ~1 us of pure latency here, and fp32 is what batch_norm_stats itself uses)
+    const double inv_n = (double)(1.0f / local_count);
+    const double mean = sm * inv_n;
+    double var = sq * inv_n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    lmean = (float)mean;
+    linvstd = 1.0f / sqrtf((float)var + a.eps);
+    lvar_unb = (float)var * (local_count / (local_count - 1.0f));
+  }
+}
+
+// The all_gather of _functions.py:74 as pushed tagged words: this rank's (mean, invstd, unbiased var, count) into
+// slot [rank] of every rank's region -- its own included, which is how the other CTAs of this grid get them.
+template <int C>
+__device__ __forceinline__ void bn_push_stats(const BnPoolArgs& a, int c, float lmean, float linvstd, float lvar_unb,
+                                              float local_count, unsigned int tag, bool self_too) {
+  for (int q = 0; q < a.comm.world; ++q) {
+    if (q == a.comm.rank && !self_too) continue;
+    llword* slot = a.comm.peer[q]->ll_bn_fwd[a.layer][a.comm.rank];
+    ll_store(&slot[c], lmean, tag);
+    ll_store(&slot[C + c], linvstd, tag);
+    ll_store(&slot[2 * C + c], lvar_unb, tag);
+    if (c == 0) ll_store(&slot[3 * C], local_count, tag);
+  }
+}
+
+// Small grids, `a.ll`: CTA 0 of the BN kernel calls this BEFORE it waits for the grid dependency.  Under
+// programmatic launch this grid is resident while the conv kernel is still finishing, so CTA 0 picks the tagged
+// partial rows up as they land, and this rank's statistics are on their way to the peers (one NVLink latency)
+// while the kernel boundary is still being crossed.  The other CTAs never touch the rows: after their wait they
+// poll the published words of all ranks.  Without the overlap (plain launches) the rows are simply there already.
+template <int C>
+__device__ void bn_forward_publish(const BnPoolArgs& a, float local_count) {
+  const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
+  float lmean = 0.f, linvstd = 0.f, lvar_unb = 0.f;
+  bn_local_stats<C, true>(a, local_count, tag, lmean, linvstd, lvar_unb);
+  if (threadIdx.x < C) bn_push_stats<C>(a, threadIdx.x, lmean, linvstd, lvar_unb, local_count, tag, true);
+}
 
 template <int C>
 __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_invstd, int rm_off, int rv_off,
                                  float local_count) {
   const int c = threadIdx.x;
   const bool xchg = !a.eval && a.sync && a.comm.world > 1;
-  const bool defer = !a.eval && a.part != nullptr;
+  const bool defer = !a.eval && a.part != nullptr && !a.ll;
+  const bool polled = !a.eval && a.ll;
   float lmean = 0.f, linvstd = 0.f, lvar_unb = 0.f;
   if (defer) {
-    // local statistics from the partial rows: column = (channel, stat), several row lanes per column
-    __shared__ double fin[512];
-    constexpr int COLS = 2 * C;
-    const int lanes = min((int)blockDim.x / COLS, 512 / COLS);
-    const int col = c % COLS, lane = c / COLS;
-    if (lane < lanes) {
-      // deferred mode means at most 64 rows: every load of this thread is issued before the first one is
-      // consumed (ONE trip to L2 instead of rows / lanes / 4 of them); the sum keeps its row order
-      constexpr int NV = 64 / (256 / COLS);
-      float v[NV];
-#pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        const int r = lane + i * lanes;
-        v[i] = r < a.rows ? __ldcg(&a.part[(size_t)r * COLS + col]) : 0.f;
-      }
-      double acc = 0.0;
-#pragma unroll
-      for (int i = 0; i < NV; ++i) acc += (double)v[i];
-      for (int r = lane + NV * lanes; r < a.rows; r += lanes) acc += (double)__ldcg(&a.part[(size_t)r * COLS + col]);
-      fin[lane * COLS + col] = acc;
-    }
-    __syncthreads();
-    if (c < C) {
-      double sm = 0.0, sq = 0.0;
-      for (int l = 0; l < lanes; ++l) { sm += fin[l * COLS + 2 * c]; sq += fin[l * COLS + 2 * c + 1]; }
-      // sums are combined in double; the few divisions / the square root run in fp32 (an fp64 divide and
-      // sqrt chain costs ~1 us of pure latency here, and fp32 is what batch_norm_stats itself uses)
-      const double inv_n = (double)(1.0f / local_count);
-      const double mean = sm * inv_n;
-      double var = sq * inv_n - mean * mean;
-      if (var < 0.0) var = 0.0;
-      lmean = (float)mean;
-      linvstd = 1.0f / sqrtf((float)var + a.eps);
-      lvar_unb = (float)var * (local_count / (local_count - 1.0f));
-      if (xchg && blockIdx.x == 0) {  // the all_gather of _functions.py:74: CTA 0 pushes self-validating words
-        const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
-        for (int q = 0; q < a.comm.world; ++q) {
-          llword* slot = a.comm.peer[q]->ll_bn_fwd[a.layer][a.comm.rank];
-          ll_store(&slot[c], lmean, tag);
-          ll_store(&slot[C + c], linvstd, tag);
-          if (c == 0) ll_store(&slot[2 * C], local_count, tag);
-        }
-      }
+    bn_local_stats<C, false>(a, local_count, 0u, lmean, linvstd, lvar_unb);
+    if (c < C && xchg && blockIdx.x == 0)
+      bn_push_stats<C>(a, c, lmean, linvstd, lvar_unb, local_count, (unsigned int)a.ds->epoch + 1u, true);
+  } else if (polled) {
+    if (c < C && !xchg) {  // single rank: the words CTA 0 published for this rank
+      float got[3];
+      const int idx[3] = {c, C + c, 2 * C + c};
+      ll_gather<3, 1>(&a.comm.self->ll_bn_fwd[a.layer][a.comm.rank][0], BN_FWD_SLOT, idx, 0, 1,
+                      (unsigned int)a.ds->epoch + 1u, got, &a.ds->error);
+      lmean = got[0]; linvstd = got[1]; lvar_unb = got[2];
     }
   } else if (!a.eval && c < C) {
     lmean = a.st->lmean[c];
@@ -346,8 +410,8 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
       float m = 0.f, m2 = 0.f, n = 0.f;
       const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
       float got[MAX_WORLD * 3];
-      const int idx[3] = {c, C + c, 2 * C};
-      ll_gather<3>(&a.comm.self->ll_bn_fwd[a.layer][0][0], 72, idx, 0, a.comm.world, tag, got, &a.ds->error);
+      const int idx[3] = {c, C + c, 3 * C};
+      ll_gather<3>(&a.comm.self->ll_bn_fwd[a.layer][0][0], BN_FWD_SLOT, idx, 0, a.comm.world, tag, got, &a.ds->error);
 #pragma unroll
       for (int r = 0; r < MAX_WORLD; ++r) {
         if (r >= a.comm.world) break;
@@ -395,6 +459,7 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
     s_g[threadIdx.x] = a.params[OFF_G + threadIdx.x];
     s_b[threadIdx.x] = a.params[OFF_BE + threadIdx.x];
   }
+  if (a.ll && !a.eval && blockIdx.x == 0) bn_forward_publish<C>(a, (float)a.B * (float)(H * H));
   pdl_sync();  // predecessor: the conv kernel that produced y and the partial statistics
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   T* __restrict__ p = reinterpret_cast<T*>(a.p);
@@ -465,6 +530,7 @@ __global__ void __launch_bounds__(256) k_bn1_relu_pool_planes(BnPoolArgs a) {
     s_g[threadIdx.x] = a.params[OFF_G1 + threadIdx.x];
     s_b[threadIdx.x] = a.params[OFF_BE1 + threadIdx.x];
   }
+  if (a.ll && !a.eval && blockIdx.x == 0) bn_forward_publish<C>(a, (float)a.B * (float)(H * H));
   pdl_sync();
   bn_forward_stats<C>(a, s_mean, s_invstd, BNB_RM1, BNB_RV1, (float)a.B * (float)(H * H));
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
@@ -522,6 +588,7 @@ __global__ void __launch_bounds__(128) k_conv14(Conv14Args a) {
   __shared__ float red[112][2];
   const int tid = threadIdx.x;
   const int cog = blockIdx.y;
+  const unsigned int ll_tag = MODE == 0 ? (unsigned int)a.ds->epoch + 1u : 0u;
   const T* __restrict__ in = reinterpret_cast<const T*>(a.in);
   T* __restrict__ out = reinterpret_cast<T*>(a.out);
 
@@ -602,7 +669,7 @@ __global__ void __launch_bounds__(128) k_conv14(Conv14Args a) {
       const int cl = tid >> 1, stat = tid & 1;
       float v = 0.f;
       for (int i = 0; i < 14; ++i) v += red[cl * 14 + i][stat];
-      a.part[((size_t)blockIdx.x * 32 + cog * 8 + cl) * 2 + stat] = v;
+      store_partial(a.part, ((size_t)blockIdx.x * 32 + cog * 8 + cl) * 2 + stat, v, a.defer == 2, ll_tag);
     }
     if (!a.defer && last_cta_done(&a.ds->ticket[1], gridDim.x * gridDim.y))
       finalize_fwd_stats<32>(a.part, gridDim.x, (float)a.B * 196.f, a.eps, a.st, 1, a.comm, a.ds, a.sync);
