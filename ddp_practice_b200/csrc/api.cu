@@ -510,7 +510,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   k_reduce_rows<<<25, 128, 0, s2>>>(c->gpart, c->gred, gw_rows); mark();
   if (fork) cudaEventRecord(c->ev_j2, s2);
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
-  const int ns1 = clampi(cdiv(B, 2), 1, 32);
+  const int ns1 = clampi(B, 1, 32);  // one image per CTA at small batch: every thread has a single window, a single trip to L2
   BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->defer_stats == 2 ? c->bpart1_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, c->defer_stats, ns1, nullptr, nullptr, c->gpart};
   launch_k(k_bn_bwd_reduce<T, 16, 28>, dim3(16, ns1), dim3(256), 0, s, r1, pdl); mark();
   const int gc1 = std::min(B, 296);

@@ -258,7 +258,10 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
   }
   if (c < C) {
     float s0, s1;
-    if (polled && !xchg) {  // single rank: the words CTA (0,0) published
+    if (polled && !xchg && first) {  // single rank, the publishing CTA: it has the sums already
+      s0 = s_loc[c];
+      s1 = s_loc[C + c];
+    } else if (polled && !xchg) {  // single rank: the words CTA (0,0) published
       float got[2];
       const int idx[2] = {c, C + c};
       ll_gather<2, 1>(&a.comm.self->ll_bn_bwd[a.layer][a.comm.rank][0], 64, idx, 0, 1, tag, got, &a.ds->error);
@@ -573,7 +576,7 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
     __syncthreads();
     if (threadIdx.x == 0) TRACE(12 * 16 + 2);
     if (tid < 140) {
-#pragma unroll 1  // rolled: less straight-line code to pull through a cold instruction cache
+#pragma unroll
       for (int hh = 0; hh < 4; ++hh) {
         const int h = hh * 7 + rs;  // lanes of a warp read consecutive rows: bank-conflict free 16-byte loads
         const float* drow = dy_s + (col * 28 + h) * 28;

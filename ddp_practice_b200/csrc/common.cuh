@@ -231,7 +231,7 @@ __device__ unsigned long long g_trace[256];  // kernel k owns slots 16k .. 16k+1
 __device__ __forceinline__ void trace_mark(int slot) {
   if (blockIdx.x == 0 && blockIdx.y == 0) {
     unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");  // the clobber keeps loads / stores on their side of the mark
     g_trace[slot] = t;
   }
 }

@@ -192,10 +192,9 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
       for (int c = 0; c < 4; ++c)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[r][c][j] = 0.f;
-    // the kh loop stays rolled on purpose: the step runs ~14 different kernels back to back, more code than the
-    // SM's instruction cache holds, so straight-line code is fetched from L2 on every launch (measured: the fully
-    // unrolled 800-FMA body ran at ~2.7 cycles per instruction)
-#pragma unroll 1
+    // fully unrolled: a rolled kh loop (8x less code) was measured 20% SLOWER, so instruction fetch is not what
+    // limits this body; one warp per scheduler issuing 3-register FFMAs is
+#pragma unroll
     for (int kh = 0; kh < 5; ++kh) {
       float in[2][8];
 #pragma unroll
@@ -367,17 +366,35 @@ __device__ __forceinline__ void bn_push_stats(const BnPoolArgs& a, int c, float 
 // partial rows up as they land, and this rank's statistics are on their way to the peers (one NVLink latency)
 // while the kernel boundary is still being crossed.  The other CTAs never touch the rows: after their wait they
 // poll the published words of all ranks.  Without the overlap (plain launches) the rows are simply there already.
-template <int C>
-__device__ void bn_forward_publish(const BnPoolArgs& a, float local_count) {
-  const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
+// What CTA 0 (the CTA that also maintains the running statistics) fetched or computed ahead of the grid dependency.
+struct BnOwn {
+  bool have = false;                               // this rank's statistics below are valid (bn_forward_publish ran)
   float lmean = 0.f, linvstd = 0.f, lvar_unb = 0.f;
-  bn_local_stats<C, true>(a, local_count, tag, lmean, linvstd, lvar_unb);
-  if (threadIdx.x < C) bn_push_stats<C>(a, threadIdx.x, lmean, linvstd, lvar_unb, local_count, tag, true);
+  float rm_old = 0.f, rv_old = 0.f;                // running mean / var of channel threadIdx.x before this step
+  long long nbt_old = 0;
+};
+
+template <int C>
+__device__ void bn_forward_publish(const BnPoolArgs& a, float local_count, BnOwn& own) {
+  const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
+  bn_local_stats<C, true>(a, local_count, tag, own.lmean, own.linvstd, own.lvar_unb);
+  if (threadIdx.x < C) bn_push_stats<C>(a, threadIdx.x, own.lmean, own.linvstd, own.lvar_unb, local_count, tag, true);
+  own.have = true;
+}
+
+// CTA 0's early work: the old running statistics (the last kernel that wrote them belongs to the previous step) and,
+// with tagged rows, the publication of this rank's statistics.  Must be called by every thread of the CTA.
+template <int C>
+__device__ __forceinline__ void bn_forward_early(const BnPoolArgs& a, int rm_off, int rv_off, float local_count, BnOwn& own) {
+  if (blockIdx.x != 0 || a.eval) return;
+  if (threadIdx.x < C) { own.rm_old = a.bnbuf[rm_off + threadIdx.x]; own.rv_old = a.bnbuf[rv_off + threadIdx.x]; }
+  if (threadIdx.x == 0) own.nbt_old = a.nbt[a.layer];
+  if (a.ll) bn_forward_publish<C>(a, local_count, own);
 }
 
 template <int C>
 __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_invstd, int rm_off, int rv_off,
-                                 float local_count) {
+                                 float local_count, const BnOwn& own) {
   const int c = threadIdx.x;
   const bool xchg = !a.eval && a.sync && a.comm.world > 1;
   const bool defer = !a.eval && a.part != nullptr && !a.ll;
@@ -388,7 +405,9 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
     if (c < C && xchg && blockIdx.x == 0)
       bn_push_stats<C>(a, c, lmean, linvstd, lvar_unb, local_count, (unsigned int)a.ds->epoch + 1u, true);
   } else if (polled) {
-    if (c < C && !xchg) {  // single rank: the words CTA 0 published for this rank
+    if (own.have) {  // CTA 0 computed them itself
+      lmean = own.lmean; linvstd = own.linvstd; lvar_unb = own.lvar_unb;
+    } else if (c < C && !xchg) {  // single rank: the words CTA 0 published for this rank
       float got[3];
       const int idx[3] = {c, C + c, 2 * C + c};
       ll_gather<3, 1>(&a.comm.self->ll_bn_fwd[a.layer][a.comm.rank][0], BN_FWD_SLOT, idx, 0, 1,
@@ -439,10 +458,10 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
       a.st->invstd[c] = invstd;
       if (c == 0) {
         a.st->n_total = n_total;
-        a.nbt[a.layer] += 1;
+        a.nbt[a.layer] = own.nbt_old + 1;
       }
-      a.bnbuf[rm_off + c] = (1.0f - a.momentum) * a.bnbuf[rm_off + c] + a.momentum * mean;
-      a.bnbuf[rv_off + c] = (1.0f - a.momentum) * a.bnbuf[rv_off + c] + a.momentum * var_unb;
+      a.bnbuf[rm_off + c] = (1.0f - a.momentum) * own.rm_old + a.momentum * mean;
+      a.bnbuf[rv_off + c] = (1.0f - a.momentum) * own.rv_old + a.momentum * var_unb;
     }
   }
   __syncthreads();
@@ -459,7 +478,8 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
     s_g[threadIdx.x] = a.params[OFF_G + threadIdx.x];
     s_b[threadIdx.x] = a.params[OFF_BE + threadIdx.x];
   }
-  if (a.ll && !a.eval && blockIdx.x == 0) bn_forward_publish<C>(a, (float)a.B * (float)(H * H));
+  BnOwn own;
+  bn_forward_early<C>(a, RM, RV, (float)a.B * (float)(H * H), own);
   pdl_sync();  // predecessor: the conv kernel that produced y and the partial statistics
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   T* __restrict__ p = reinterpret_cast<T*>(a.p);
@@ -476,7 +496,7 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
     load2<T>(src, q0, q1);
     load2<T>(src + H, q2, q3);
   }
-  bn_forward_stats<C>(a, s_mean, s_invstd, RM, RV, (float)a.B * (float)(H * H));
+  bn_forward_stats<C>(a, s_mean, s_invstd, RM, RV, (float)a.B * (float)(H * H), own);
   if (threadIdx.x == 0) TRACE((C == 16 ? 2 : 4) * 16 + 1);
   auto emit = [&](size_t idx, float v0, float v1, float v2, float v3) {
     const int pw = (int)(idx % HP), ph = (int)((idx / HP) % HP);
@@ -530,9 +550,10 @@ __global__ void __launch_bounds__(256) k_bn1_relu_pool_planes(BnPoolArgs a) {
     s_g[threadIdx.x] = a.params[OFF_G1 + threadIdx.x];
     s_b[threadIdx.x] = a.params[OFF_BE1 + threadIdx.x];
   }
-  if (a.ll && !a.eval && blockIdx.x == 0) bn_forward_publish<C>(a, (float)a.B * (float)(H * H));
+  BnOwn own;
+  bn_forward_early<C>(a, BNB_RM1, BNB_RV1, (float)a.B * (float)(H * H), own);
   pdl_sync();
-  bn_forward_stats<C>(a, s_mean, s_invstd, BNB_RM1, BNB_RV1, (float)a.B * (float)(H * H));
+  bn_forward_stats<C>(a, s_mean, s_invstd, BNB_RM1, BNB_RV1, (float)a.B * (float)(H * H), own);
   const T* __restrict__ y = reinterpret_cast<const T*>(a.y);
   T* __restrict__ pl = reinterpret_cast<T*>(a.p_planes);
   const size_t total = (size_t)a.B * 2 * 196;

@@ -83,6 +83,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   const int W = a.comm.world, rank = a.comm.rank;
   const unsigned long long epoch = a.ds->epoch;
   const float scale = a.ds->scale;
+  const int tracker = a.ds->growth_tracker;
   if (tid == 0) s_nonfinite = 0;
   // parameters are fetched now, long before they are needed, so the load overlaps everything below
   float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -107,11 +108,17 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   if (cta == 0) {
     const int e4 = tid % 104, rl = tid / 104;
     if (rl < 9) {
+      // four predicated loads per trip, never a one-load-at-a-time remainder loop (a partially unrolled loop with
+      // a run-time trip count gets one, and each of its loads is a full trip to L2)
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-      for (int r = rl; r < a.rows_conv1; r += 9) {
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(a.gpart + (size_t)r * N_PAD + 4 * e4));
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      for (int r0 = rl; r0 < a.rows_conv1; r0 += 36) {
+        float4 v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          v[i] = r0 + 9 * i < a.rows_conv1 ? __ldcg(reinterpret_cast<const float4*>(a.gpart + (size_t)(r0 + 9 * i) * N_PAD + 4 * e4))
+                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { acc.x += v[i].x; acc.y += v[i].y; acc.z += v[i].z; acc.w += v[i].w; }
       }
       s_c1[rl][e4] = acc;
     }
@@ -145,10 +152,13 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
           g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
         }
       }
-#pragma unroll 8
-      for (int r = 0; r < rows; ++r) {
-        const float4 v = __ldcg(reinterpret_cast<const float4*>(p + (size_t)r * N_PAD));
-        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+      for (int r0 = 0; r0 < rows; r0 += 4) {  // four predicated loads per trip (see above)
+        float4 v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          v[i] = r0 + i < rows ? __ldcg(reinterpret_cast<const float4*>(p + (size_t)(r0 + i) * N_PAD)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { g.x += v[i].x; g.y += v[i].y; g.z += v[i].z; g.w += v[i].w; }
       }
       g.x = rnd<T>(g.x); g.y = rnd<T>(g.y); g.z = rnd<T>(g.z); g.w = rnd<T>(g.w);
     } else {
@@ -265,7 +275,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
           a.ds->scale = scale * a.backoff_factor;
           a.ds->growth_tracker = 0;
         } else {
-          const int t = a.ds->growth_tracker + 1;
+          const int t = tracker + 1;
           if (t == a.growth_interval) {
             const float grown = scale * a.growth_factor;
             if (isfinite(grown)) a.ds->scale = grown;
