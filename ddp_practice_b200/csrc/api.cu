@@ -371,6 +371,15 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
     }
     c->launches++;
   };
+  auto skip_slot = [&]() {  // keeps the profile's 15 slots aligned: an empty slot for a kernel that did not run
+    if (rec && rec->events) {
+      cudaEvent_t ev;
+      cudaEventCreate(&ev);
+      if (rec->ev_external) cudaEventRecordWithFlags(ev, rec->ev_stream, cudaEventRecordExternal);
+      else cudaEventRecord(ev, rec->ev_stream);
+      rec->events->push_back(ev);
+    }
+  };
   // the two weight-gradient branches and the filter-tile refresh do not sit on the activation chain:
   // they run on side streams (parallel branches of the captured graph)
   const bool fork = !(rec && rec->events);  // per-kernel profiling keeps everything on one stream
@@ -388,12 +397,8 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
     if constexpr (!std::is_same<T, float>::value) k_refresh_w2_tiles<T><<<100, 256, 0, s1>>>(c->params, c->w2_tiles);
     mark();
     if (fork) cudaEventRecord(c->ev_j0, s1);
-  } else if (rec && rec->events) {  // keep the profile's 15 slots aligned: an empty slot for the kernel that did not run
-    cudaEvent_t ev;
-    cudaEventCreate(&ev);
-    if (rec->ev_external) cudaEventRecordWithFlags(ev, rec->ev_stream, cudaEventRecordExternal);
-    else cudaEventRecord(ev, rec->ev_stream);
-    rec->events->push_back(ev);
+  } else {
+    skip_slot();
   }
   // 1. conv1 + local BN1 statistics
   const int g1 = std::min(B, 296);
@@ -451,8 +456,10 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
                 defer2 == 2 ? c->part2_ll : defer2 ? c->part2 : nullptr, tc ? g2 * tsplit : g2, defer2 == 2};
   launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark();
   // 5. Linear + CE + dlogits + d(pool2 out)
+  // small batch: BN2's backward pass 1 rides in this kernel (one image per CTA, one tagged partial row per image)
+  const bool fuse_bn2r = c->defer_stats == 2 && B <= 64;
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, c->dlogits, c->dflat, c->nll, c->counts,
-           c->ds, B, cfg.use_scaler, 0};
+           c->ds, B, cfg.use_scaler, 0, c->y2, st2, fuse_bn2r ? c->bpart2_ll : nullptr};
   if (rec) rec->a_fc = f;
   if (B > 1184) launch_k(k_fc_ce<T, 4>, dim3(296), dim3(224), 0, s, f, pdl);
   else launch_k(k_fc_ce<T, 1>, dim3(std::min(B, 296)), dim3(224), 0, s, f, pdl);
@@ -464,13 +471,15 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   k_fc_wgrad<T><<<dim3(7, nsf), 224, 0, s1>>>(fw); mark();
   if (fork) cudaEventRecord(c->ev_j1, s1);
   // 7/8. BN2 backward: reduce, then d(conv2 out)
-  const int ns2 = clampi(cdiv(B, 4), 1, 16);
-  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->defer_stats == 2 ? c->bpart2_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->defer_stats, ns2, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
+  const int ns2 = clampi(cdiv(B, 4), 1, 16);  // batch splits of the two BN2 backward kernels
+  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->defer_stats == 2 ? c->bpart2_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->defer_stats,
+               fuse_bn2r ? B : ns2 /* partial rows per channel */, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
   // the plane-writing apply kernel has 4 channel groups per batch split: use more splits to fill the GPU
   const int ns2p = clampi(cdiv(B, 2), 1, 64);
   BnBwdArgs r2p = r2;
   r2p.per_split = cdiv(B, ns2p);
-  launch_k(k_bn_bwd_reduce<T, 32, 14>, dim3(32, ns2), dim3(256), 0, s, r2, pdl); mark();
+  if (!fuse_bn2r) { launch_k(k_bn_bwd_reduce<T, 32, 14>, dim3(32, ns2), dim3(256), 0, s, r2, pdl); mark(); }
+  else skip_slot();
   if (planes) {
     if constexpr (!std::is_same<T, float>::value) launch_k(k_bn2_bwd_apply_planes<T>, dim3(4, ns2p), dim3(256), 0, s, r2p, pdl);
   } else {
@@ -583,7 +592,8 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const BatchSrc& x, const int64_t
   mark();
   BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps, nullptr, 0};
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
-  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1};
+  FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1,
+           nullptr, nullptr, nullptr};
   if (rec) rec->a_fc = f;
   if (B > 1184) k_fc_ce<T, 4><<<296, 224, 0, s>>>(f);
   else k_fc_ce<T, 1><<<std::min(B, 296), 224, 0, s>>>(f);

@@ -7,22 +7,6 @@
 
 namespace dstep {
 
-// The four BN outputs of one 2x2 pooling window and who wins the pool.
-// Winner = first maximum of the ReLU outputs in scan order (max_pool2d_with_indices);
-// gradient flows only if the winner's ReLU output is > 0 (threshold_backward).
-template <typename T>
-__device__ __forceinline__ int pool_winner(const float y[4], float mu, float is, float g, float b, bool& live) {
-  float best = -1.f;
-  int arg = 0;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float r = fmaxf(rnd<T>((y[i] - mu) * is * g + b), 0.f);
-    if (r > best) { best = r; arg = i; }
-  }
-  live = best > 0.f;
-  return arg;
-}
-
 // ---------------------------------------------------------------------------------------
 // fc weight / bias gradient: dW[j][k] = sum_n dlogits[n][j] * p2[n][k], db[j] = sum_n dlogits[n][j]
 // grid (7 k-chunks of 224, NS batch splits); partial rows go to gpart[split].
@@ -126,7 +110,8 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
       const int arg = pool_winner<T>(v[u], mu, is, g, b, live);
       if (live) {
         sdy += d[u];
-        sdyx = fmaf(d[u], v[u][arg] - mu, sdyx);
+        const float win = arg == 0 ? v[u][0] : arg == 1 ? v[u][1] : arg == 2 ? v[u][2] : v[u][3];  // selects, not a dynamic index
+        sdyx = fmaf(d[u], win - mu, sdyx);
       }
     }
   }
@@ -141,7 +126,8 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
     const int arg = pool_winner<T>(v, mu, is, g, b, live);
     if (live) {
       sdy += d;
-      sdyx = fmaf(d, v[arg] - mu, sdyx);
+      const float win = arg == 0 ? v[0] : arg == 1 ? v[1] : arg == 2 ? v[2] : v[3];
+      sdyx = fmaf(d, win - mu, sdyx);
     }
   }
   sdy = warp_sum(sdy);
@@ -183,8 +169,10 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
 
 // Global (all-rank) backward sums for the consumer of pass 1: k1 = sum_dy / N,
 // k2 = invstd^2 * sum_dy_xmu / N  (`batch_norm_backward_elemt`, _functions.py:170).
-template <int C>
-__device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
+// `after_wait()` runs right after the grid dependency resolved and before the sums are polled: the place for the
+// caller's loads of what the direct predecessor wrote, so that they travel together with the polls.
+template <int C, typename AfterWait>
+__device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, AfterWait&& after_wait) {
   constexpr int OFF_G = (C == 16) ? OFF_G1 : OFF_G2, OFF_BE = (C == 16) ? OFF_BE1 : OFF_BE2;
   __shared__ float s_loc[2 * C];
   const int c = threadIdx.x;
@@ -252,6 +240,7 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
     publish(true);
   }
   pdl_sync();  // predecessor: pass 1 (bpart)
+  after_wait();
   if (a.defer == 1) {
     local_sums(false);
     if (first) publish(xchg);
@@ -288,6 +277,11 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
   __syncthreads();
 }
 
+template <int C>
+__device__ __forceinline__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2) {
+  bn_backward_sums<C>(a, s_k1, s_k2, [] {});
+}
+
 // BN backward, pass 2 for layer 2: d(conv2 out) materialised (it feeds both conv2 dgrad and
 // wgrad); also the conv2 bias gradient partials (sum of the rounded values).  grid (32, NS).
 template <typename T>
@@ -302,9 +296,10 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
   const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
   T* __restrict__ dy = reinterpret_cast<T*>(a.dy);
   const int total = max(0, n1 - n0) * HP * HP;
-  // Everything this thread's first window needs except the two sums is older than the predecessor's
-  // predecessor (a kernel is only launched once every CTA of the one before it has passed ITS wait), so it is
-  // fetched before the wait inside bn_backward_sums: one trip to L2 for the sums and the data together
+  // The conv output and the BN statistics of this thread's first window are older than the predecessor's
+  // predecessor (a kernel is only launched once every CTA of the one before it has passed ITS wait), so they are
+  // fetched before the wait inside bn_backward_sums; the incoming gradient may come from the direct predecessor
+  // (pass 1 fused into the Linear/CE kernel) and is fetched right after the wait, together with the polls
   const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G2 + c], b = a.params[OFF_BE2 + c];
   float pv[4] = {0.f, 0.f, 0.f, 0.f}, pd = 0.f;
   if (tid < total) {
@@ -312,9 +307,10 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
     const size_t off = (((size_t)n * C + c) * H + 2 * ph) * H + 2 * pw;
     load2<T>(y + off, pv[0], pv[1]);
     load2<T>(y + off + H, pv[2], pv[3]);
-    pd = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
   }
-  bn_backward_sums<C>(a, s_k1, s_k2);
+  bn_backward_sums<C>(a, s_k1, s_k2, [&] {
+    if (tid < total) pd = ldf<T>(&dp[((size_t)(n0 + tid / (HP * HP)) * C + c) * HP * HP + tid % (HP * HP)]);
+  });
   if (threadIdx.x == 0) TRACE(9 * 16 + 1);
   const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
   float bsum = 0.f;

@@ -224,6 +224,22 @@ __device__ __forceinline__ bool last_cta_done(unsigned int* ticket, unsigned int
   return s_last != 0;
 }
 
+// The four BN outputs of one 2x2 pooling window and who wins the pool.
+// Winner = first maximum of the ReLU outputs in scan order (max_pool2d_with_indices);
+// gradient flows only if the winner's ReLU output is > 0 (threshold_backward).
+template <typename T>
+__device__ __forceinline__ int pool_winner(const float y[4], float mu, float is, float g, float b, bool& live) {
+  float best = -1.f;
+  int arg = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float r = fmaxf(rnd<T>((y[i] - mu) * is * g + b), 0.f);
+    if (r > best) { best = r; arg = i; }
+  }
+  live = best > 0.f;
+  return arg;
+}
+
 // Optional in-kernel phase timestamps (build with -DDDPSTEP_TRACE): CTA 0 writes globaltimer values
 // into a small global buffer so latency chains inside a kernel can be read off directly.
 #ifdef DDPSTEP_TRACE

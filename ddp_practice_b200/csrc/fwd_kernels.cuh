@@ -713,6 +713,12 @@ struct FcArgs {
   float* counts;         // [2] correct,size  (eval)
   const DevState* ds;
   int B, use_scaler, eval;
+  // Small batch (one image per CTA): BN2's backward pass 1 (`batch_norm_backward_reduce`, _functions.py:144) rides
+  // along -- the gradient at the pool output is in this kernel's registers anyway -- and leaves one tagged partial
+  // row per image in bpart2 ([32][B][2], see BnBwdArgs in bwd_kernels.cuh).  bpart2 == nullptr: separate kernel.
+  const void* y2;       // conv2 output [B,32,14,14]
+  const BnStat* st2;    // BN2 statistics of this step
+  float* bpart2;
 };
 
 // NI = images per loop iteration: 1 at small batch (shortest chain), 4 at large batch (the two block-wide
@@ -732,8 +738,29 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
   float b[10];
 #pragma unroll
   for (int j = 0; j < 10; ++j) b[j] = rnd<T>(a.params[OFF_BFC + j]);
+  // fused BN2 backward pass 1: this thread's seven pooling windows of conv2's output (two launches old, so they may
+  // be fetched before the wait)
+  const bool fuse = NI == 1 && a.bpart2 != nullptr && (int)blockIdx.x < a.B;
+  float yw[7][4];
+  unsigned int ll_tag = 0u;
+  if (fuse) {
+    const T* __restrict__ y2 = reinterpret_cast<const T*>(a.y2);
+    ll_tag = (unsigned int)a.ds->epoch + 1u;
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+      const int k = tid + 224 * i, c = k / 49, w = k % 49, ph = w / 7, pw = w % 7;
+      const T* src = y2 + (((size_t)blockIdx.x * 32 + c) * 14 + 2 * ph) * 14 + 2 * pw;
+      load2<T>(src, yw[i][0], yw[i][1]);
+      load2<T>(src + 14, yw[i][2], yw[i][3]);
+    }
+  }
   pdl_sync();  // predecessor: BN2 + ReLU + pool (p2); the weights above do not depend on it
   if (threadIdx.x == 0) TRACE(5 * 16 + 1);
+  __shared__ float s_bn[32][4];  // BN2 mean, invstd, gamma, beta (the first two were written by the predecessor)
+  if (fuse && tid < 128) {
+    const int c = tid >> 2, q = tid & 3;
+    s_bn[c][q] = q == 0 ? a.st2->mean[c] : q == 1 ? a.st2->invstd[c] : q == 2 ? a.params[OFF_G2 + c] : a.params[OFF_BE2 + c];
+  }
   // incoming gradient of the loss: `scale` cast to the loss dtype (65536 -> inf in fp16)
   const float gl = a.use_scaler ? rnd<T>(a.ds->scale) : 1.0f;
   const float g = rnd<T>(-(gl / (float)a.B));
@@ -805,12 +832,45 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
         }
       if (tid == 0) a.nll[n] = nll;
       T* __restrict__ dflat = reinterpret_cast<T*>(a.dflat);
+      float df[7];
 #pragma unroll
       for (int i = 0; i < 7; ++i) {
         float acc = 0.f;
 #pragma unroll
         for (int j = 0; j < 10; ++j) acc = fmaf(dl[j], w[j][i], acc);
         stf<T>(&dflat[(size_t)n * 1568 + tid + 224 * i], acc);
+        df[i] = rnd<T>(acc);
+      }
+      if (fuse) {
+        // per element: the gradient reaches the BN output only through the pool winner, and only if its ReLU is open.
+        // Per channel (49 consecutive elements) the two sums are formed in a fixed order: 7 lanes of 7, then the lanes.
+        __shared__ float2 s_el[1568];
+        __shared__ float2 s_ln[32][7];
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          const int k = tid + 224 * i, c = k / 49;
+          const float mu = s_bn[c][0];
+          bool live;
+          const int arg = pool_winner<T>(yw[i], mu, s_bn[c][1], s_bn[c][2], s_bn[c][3], live);
+          const float win = arg == 0 ? yw[i][0] : arg == 1 ? yw[i][1] : arg == 2 ? yw[i][2] : yw[i][3];  // no dynamic index: registers
+          s_el[k] = live ? make_float2(df[i], df[i] * (win - mu)) : make_float2(0.f, 0.f);
+        }
+        __syncthreads();
+        {
+          const int c = tid / 7, l = tid % 7;  // 224 threads = 32 channels x 7 lanes
+          float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+          for (int q = 0; q < 7; ++q) { const float2 v = s_el[c * 49 + l * 7 + q]; acc.x += v.x; acc.y += v.y; }
+          s_ln[c][l] = acc;
+        }
+        __syncthreads();
+        if (tid < 64) {
+          const int c = tid >> 1, which = tid & 1;
+          float v = 0.f;
+#pragma unroll
+          for (int l = 0; l < 7; ++l) v += which ? s_ln[c][l].y : s_ln[c][l].x;
+          store_partial(a.bpart2, ((size_t)c * a.B + n) * 2 + which, v, 1, ll_tag);
+        }
       }
     }
     __syncthreads();
