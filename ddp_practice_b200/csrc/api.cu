@@ -39,6 +39,9 @@ struct GraphEntry {
   BatchSrc x = {nullptr, nullptr, nullptr};
   const int64_t* y = nullptr;
   int n_kernels = 0;
+  // host-fed variant (ddpstep_train_step_host): the two H2D copies are nodes of the graph
+  cudaGraphNode_t node_hx = nullptr, node_hy = nullptr;
+  const void *hx = nullptr, *hy = nullptr;
 };
 
 struct ddpstep_ctx {
@@ -73,6 +76,7 @@ struct ddpstep_ctx {
   std::map<long, GraphEntry> graphs;
   cudaStream_t cap_stream = nullptr, side1 = nullptr, side2 = nullptr;
   cudaEvent_t ev_f0 = nullptr, ev_j0 = nullptr, ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
+  cudaEvent_t ev_h0 = nullptr, ev_h1 = nullptr;
   float* gred = nullptr;
   volatile float* host_mail = nullptr;  // pinned, mapped: {loss, completed-step counter}
   unsigned int steps_enqueued = 0;     // training steps launched so far (matches DevState.epoch once they finish)
@@ -179,7 +183,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) { void* hm = nullptr; e = cudaHostAlloc(&hm, 64, cudaHostAllocMapped); if (e == cudaSuccess) { memset(hm, 0, 64); ctx->host_mail = static_cast<volatile float*>(hm); } }
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side1, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side2, cudaStreamNonBlocking);
-  for (cudaEvent_t* ev : {&ctx->ev_f0, &ctx->ev_j0, &ctx->ev_f1, &ctx->ev_j1, &ctx->ev_f2, &ctx->ev_j2})
+  for (cudaEvent_t* ev : {&ctx->ev_f0, &ctx->ev_j0, &ctx->ev_f1, &ctx->ev_j1, &ctx->ev_f2, &ctx->ev_j2, &ctx->ev_h0, &ctx->ev_h1})
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
   // kernels that need more than 48 KB of dynamic shared memory
   const int smem_dgrad = (32 * 18 * C14_RS + 8 * 32 * 25) * 4;
@@ -235,7 +239,7 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
   if (ctx->side1) cudaStreamDestroy(ctx->side1);
   if (ctx->side2) cudaStreamDestroy(ctx->side2);
-  for (cudaEvent_t ev : {ctx->ev_f0, ctx->ev_j0, ctx->ev_f1, ctx->ev_j1, ctx->ev_f2, ctx->ev_j2}) if (ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : {ctx->ev_f0, ctx->ev_j0, ctx->ev_f1, ctx->ev_j1, ctx->ev_f2, ctx->ev_j2, ctx->ev_h0, ctx->ev_h1}) if (ev) cudaEventDestroy(ev);
   delete ctx;
   return 0;
 }
@@ -695,6 +699,68 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
   return 0;
 }
 
+static bool is_pinned_host(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
+// The training step fed from pinned host memory as ONE graph: the two H2D copies are root nodes (the label copy on
+// a parallel branch), conv1 depends on both, the rest is the usual step.  Against two cudaMemcpyAsync calls plus a
+// graph launch this saves two driver calls on the host and the stream-order gaps between three separately
+// submitted pieces of work.  A new pair of host pointers re-points the two copy nodes of the instantiated graph.
+static int run_graph_host(ddpstep_ctx* ctx, const float* xh, const int64_t* yh, int B, cudaStream_t s) {
+  const long key = 20000000L + B;
+  const size_t xb = (size_t)B * 784 * 4, yb = (size_t)B * 8;
+  auto it = ctx->graphs.find(key);
+  if (it == ctx->graphs.end()) {
+    GraphEntry ge;
+    Recorder rec;
+    const int64_t before = ctx->launches;
+    CK(cudaStreamBeginCapture(ctx->cap_stream, cudaStreamCaptureModeThreadLocal));
+    cudaEventRecord(ctx->ev_h0, ctx->cap_stream);
+    cudaStreamWaitEvent(ctx->side1, ctx->ev_h0, 0);
+    cudaMemcpyAsync(ctx->y_stage, yh, yb, cudaMemcpyHostToDevice, ctx->side1);
+    cudaEventRecord(ctx->ev_h1, ctx->side1);
+    cudaMemcpyAsync(ctx->x_stage, xh, xb, cudaMemcpyHostToDevice, ctx->cap_stream);
+    cudaStreamWaitEvent(ctx->cap_stream, ctx->ev_h1, 0);
+    cudaError_t e = enqueue<true>(ctx, BatchSrc{ctx->x_stage, nullptr, nullptr}, ctx->y_stage, B, ctx->cap_stream, &rec);
+    cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &ge.graph);
+    ctx->launches = before;
+    if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "launch during capture failed: %s", cudaGetErrorString(e));
+    if (e2 != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "graph capture failed: %s", cudaGetErrorString(e2));
+    CK(cudaGraphInstantiate(&ge.exec, ge.graph, 0));
+    size_t n = 0;
+    CK(cudaGraphGetNodes(ge.graph, nullptr, &n));
+    std::vector<cudaGraphNode_t> nodes(n);
+    CK(cudaGraphGetNodes(ge.graph, nodes.data(), &n));
+    for (cudaGraphNode_t nd : nodes) {
+      cudaGraphNodeType ty;
+      CK(cudaGraphNodeGetType(nd, &ty));
+      if (ty != cudaGraphNodeTypeMemcpy) continue;
+      cudaMemcpy3DParms mp;
+      CK(cudaGraphMemcpyNodeGetParams(nd, &mp));
+      if (mp.dstPtr.ptr == ctx->x_stage) ge.node_hx = nd;
+      else if (mp.dstPtr.ptr == ctx->y_stage) ge.node_hy = nd;
+    }
+    if (!ge.node_hx || !ge.node_hy) return fail(ctx, DDPSTEP_E_STATE, "could not locate the copy nodes in the captured graph");
+    ge.hx = xh; ge.hy = yh; ge.n_kernels = rec.n;
+    it = ctx->graphs.emplace(key, ge).first;
+  }
+  GraphEntry& ge = it->second;
+  if (ge.hx != xh) {
+    CK(cudaGraphExecMemcpyNodeSetParams1D(ge.exec, ge.node_hx, ctx->x_stage, xh, xb, cudaMemcpyHostToDevice));
+    ge.hx = xh;
+  }
+  if (ge.hy != yh) {
+    CK(cudaGraphExecMemcpyNodeSetParams1D(ge.exec, ge.node_hy, ctx->y_stage, yh, yb, cudaMemcpyHostToDevice));
+    ge.hy = yh;
+  }
+  CK(cudaGraphLaunch(ge.exec, s));
+  ctx->launches += ge.n_kernels;
+  return 0;
+}
+
 static int check_step_args(ddpstep_ctx* ctx, const void* x, int32_t batch) {
   if (!ctx) return DDPSTEP_E_ARG;
   if (!x) return fail(ctx, DDPSTEP_E_ARG, "null input pointer");
@@ -783,14 +849,23 @@ extern "C" int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* xh, const 
   static const bool zero_copy = [] { const char* e = getenv("DDPSTEP_ZEROCOPY"); return e && e[0] == '1'; }();
   const float* xd = zero_copy ? static_cast<const float*>(mapped_device_pointer(xh)) : nullptr;
   const int64_t* yd = zero_copy ? static_cast<const int64_t*>(mapped_device_pointer(yh)) : nullptr;
-  if (xd == nullptr || yd == nullptr) {  // stage through the library's device buffers (fixed graph pointers)
+  // pinned batches: copies and step as one graph.  DDPSTEP_HOSTGRAPH=0 keeps the separate copies for comparison.
+  static const bool host_graph = [] { const char* e = getenv("DDPSTEP_HOSTGRAPH"); return !(e && e[0] == '0'); }();
+  if (!zero_copy && host_graph && ctx->cfg.use_graph && is_pinned_host(xh) && is_pinned_host(yh)) {
+    ctx->steps_enqueued++;
+    rc = run_graph_host(ctx, xh, yh, batch, s);
+    if (rc) return rc;
+    xd = nullptr;
+  } else if (xd == nullptr || yd == nullptr) {  // stage through the library's device buffers (fixed graph pointers)
     CK(cudaMemcpyAsync(ctx->x_stage, xh, (size_t)batch * 784 * 4, cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(ctx->y_stage, yh, (size_t)batch * 8, cudaMemcpyHostToDevice, s));
     xd = ctx->x_stage;
     yd = ctx->y_stage;
   }
-  rc = ddpstep_train_step(ctx, xd, yd, batch, stream);
-  if (rc) return rc;
+  if (xd != nullptr) {
+    rc = ddpstep_train_step(ctx, xd, yd, batch, stream);
+    if (rc) return rc;
+  }
   if (loss_out) {
     // the tail kernel posts {loss, step counter} into pinned host memory: poll it instead of copying back and
     // synchronising the stream; fall back to a real synchronisation if nothing shows up (device error)
