@@ -334,6 +334,7 @@ struct Recorder {  // keeps the argument structs that hold x / y so graph replay
   std::vector<cudaEvent_t>* events = nullptr;  // profiling: one event after every kernel
   cudaStream_t ev_stream = nullptr;
   bool ev_external = false;
+  unsigned int skipped = 0;  // bit i: profile slot i belongs to a kernel that did not run (its work rides in another one)
   Conv1Args a_c1;
   FcArgs a_fc;
   Conv1WgradArgs a_c1w;
@@ -377,6 +378,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   };
   auto skip_slot = [&]() {  // keeps the profile's 15 slots aligned: an empty slot for a kernel that did not run
     if (rec && rec->events) {
+      rec->skipped |= 1u << rec->events->size();
       cudaEvent_t ev;
       cudaEventCreate(&ev);
       if (rec->ev_external) cudaEventRecordWithFlags(ev, rec->ev_stream, cudaEventRecordExternal);
@@ -1007,6 +1009,7 @@ extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int6
   cudaEvent_t prev = ev0;
   for (size_t i = 0; i < evs.size() && i < (size_t)kTrainKernels; ++i) {
     CK(cudaEventElapsedTime(&ms_out[i], prev, evs[i]));
+    if (rec.skipped >> i & 1u) ms_out[i] = -ms_out[i];  // nothing ran in this slot: minus the bare event-to-event interval
     prev = evs[i];
   }
   cudaEventDestroy(ev0);

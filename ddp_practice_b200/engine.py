@@ -200,7 +200,8 @@ class Engine:
         return out.float()
 
     def profile_step(self, x: torch.Tensor, y: torch.Tensor, in_graph: bool = True):
-        """One training step with per-kernel device timing: {kernel name: ms}."""
+        """One training step with per-kernel device timing: {kernel name: ms}.  A negative value = that kernel did not
+        run at this batch (its work is fused into another one); its magnitude is the bare event-to-event interval."""
         ms = (C.c_float * 16)()
         self._check(self.lib.ddpstep_profile_step(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0], int(in_graph),
                                                   ms, 16, self._stream()))

@@ -146,8 +146,12 @@ int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* host, int64_t
  * CUDA event after each of its kernels (ddpstep_kernel_name lists them; n_out >= 16 is always
  * enough) and return their device durations in ms.
  * in_graph = 1 replays the step as a graph with event-record nodes between the kernel nodes
- * (what the hot path does), 0 launches eagerly.  No reference counterpart: the reference
- * has no per-kernel instrumentation.                                  */
+ * (what the hot path does), 0 launches eagerly.  A NEGATIVE entry marks a kernel that does
+ * not run at this batch size (its work rides in another kernel: the filter-tile refresh in
+ * conv1, BN2's backward reduction in Linear+CE); its magnitude is the bare interval between
+ * two consecutive event records, i.e. the instrumentation overhead contained in every other
+ * entry.  No reference counterpart: the reference has no per-kernel instrumentation
+ * (SURVEY.md section 5).                                                                    */
 int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
                          int32_t in_graph, float* ms_out, int32_t n_out, void* stream);
 const char* ddpstep_kernel_name(int32_t i);   /* names of those kernels, "" past the end */
