@@ -296,6 +296,14 @@ def main():
                  "kernel_us": {k: round(v * 1e3, 2) for k, v in prof.items()},
                  "step_hbm_frac": (STEP_BYTES_PER_IMG_AMP * (es / 2) * B + STEP_PARAM_BYTES) / (ms_total / K * 1e-3) / 1e9 / hbm_peak,
                  "note": "batch 32 is latency-bound (SURVEY.md 8d): 7.9 MB and 0.52 GFLOP per step"})
+    # SURVEY 8(d)'s stated floor for the latency-bound case: kernel nodes on the critical path of the step graph x the
+    # measured per-node gap + one graph launch + the cross-GPU exchanges x one NVLink store-and-poll round trip
+    # (profiles/r01_microbench_launch_floor.txt; 0.7 us per PDL node, 2.05 us per graph launch, ~2.2 us per exchange)
+    crit_nodes = 10 if B <= 64 else 11
+    roof["latency_floor_us"] = {"critical_path_nodes": crit_nodes, "per_node_us": 0.7, "graph_launch_us": 2.05,
+                                "exchanges": 5 if world > 1 else 0, "per_exchange_us": 2.2,
+                                "floor_us": round(crit_nodes * 0.7 + 2.05 + (5 * 2.2 if world > 1 else 0.0), 2),
+                                "what": "launch/exchange floor only; the measured step also pays 1-2 L2 round trips per stage"}
 
     line = {"metric": METRIC, "value": world * B * K / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
