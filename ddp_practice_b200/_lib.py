@@ -19,13 +19,14 @@ class Config(C.Structure):
         ("use_graph", C.c_int32), ("conv_bias_double_round", C.c_int32),
         ("lr", C.c_float), ("init_scale", C.c_float), ("growth_factor", C.c_float), ("backoff_factor", C.c_float),
         ("growth_interval", C.c_int32), ("bn_momentum", C.c_float), ("bn_eps", C.c_float),
+        ("momentum", C.c_float), ("weight_decay", C.c_float), ("dampening", C.c_float), ("nesterov", C.c_int32),
     ]
 
 
 class Ptrs(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in (
         "params", "grads", "grads_scaled", "bn_buffers", "num_batches_tracked", "scale", "growth_tracker",
-        "found_inf", "loss", "logits", "counts", "input_stage", "label_stage")]
+        "found_inf", "loss", "logits", "counts", "input_stage", "label_stage", "momentum_buffer", "momentum_ready")]
 
 
 # every symbol include/ddpstep.h declares: (name, restype, argtypes)

@@ -78,6 +78,7 @@ struct ddpstep_ctx {
   cudaEvent_t ev_f0 = nullptr, ev_j0 = nullptr, ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
   cudaEvent_t ev_h0 = nullptr, ev_h1 = nullptr;
   float* gred = nullptr;
+  float* mom = nullptr;   // SGD momentum buffers, same flat layout as the parameters
   volatile float* host_mail = nullptr;  // pinned, mapped: {loss, completed-step counter}
   unsigned int steps_enqueued = 0;     // training steps launched so far (matches DevState.epoch once they finish)
   int64_t launches = 0;
@@ -117,6 +118,7 @@ extern "C" void ddpstep_default_config(ddpstep_config* c) {
   c->lr = 1e-4f;
   c->init_scale = 65536.0f; c->growth_factor = 2.0f; c->backoff_factor = 0.5f; c->growth_interval = 2000;
   c->bn_momentum = 0.1f; c->bn_eps = 1e-5f;
+  c->momentum = 0.f; c->weight_decay = 0.f; c->dampening = 0.f; c->nesterov = 0;
 }
 
 extern "C" const char* ddpstep_last_error(const ddpstep_ctx* ctx) {
@@ -131,6 +133,9 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
     return fail(nullptr, DDPSTEP_E_ARG, "bad rank/world %d/%d (world <= %d)", cfg->rank, cfg->world, MAX_WORLD);
   if (cfg->batch_cap < 1) return fail(nullptr, DDPSTEP_E_ARG, "batch_cap must be >= 1");
   if (cfg->dtype < 0 || cfg->dtype > 2) return fail(nullptr, DDPSTEP_E_ARG, "bad dtype");
+  if (cfg->momentum < 0.f || cfg->weight_decay < 0.f) return fail(nullptr, DDPSTEP_E_ARG, "momentum and weight_decay must be >= 0");
+  if (cfg->nesterov && (cfg->momentum <= 0.f || cfg->dampening != 0.f))
+    return fail(nullptr, DDPSTEP_E_ARG, "nesterov momentum requires a momentum and zero dampening");  // sgd.py:68
   CK(cudaSetDevice(cfg->device));
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, cfg->device));
@@ -151,7 +156,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   A(part1, 296 * 16 * 2 * 4); A(part2, 296 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
   A(part1_ll, 64 * 32 * 8); A(part2_ll, 64 * 64 * 8); A(bpart1_ll, 16 * 64 * 2 * 8); A(bpart2_ll, 32 * 64 * 2 * 8);
   A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
-  A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4);
+  A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4); A(mom, N_PAD * 4);
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
@@ -233,7 +238,7 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
                   ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->logits, ctx->dlogits, ctx->dflat, ctx->dy2, ctx->dp1,
                   ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
                   ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h, ctx->w2_tiles, ctx->gred,
-                  ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll};
+                  ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll, ctx->mom};
   for (void* p : bufs) if (p) cudaFree(p);
   if (ctx->host_mail) cudaFreeHost(const_cast<float*>(ctx->host_mail));
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
@@ -321,6 +326,7 @@ extern "C" int ddpstep_state_ptrs(ddpstep_ctx* ctx, ddpstep_ptrs* o) {
   o->found_inf = &ctx->ds->found_inf; o->loss = &ctx->ds->loss;
   o->logits = ctx->logits; o->counts = ctx->counts;
   o->input_stage = ctx->x_stage; o->label_stage = ctx->y_stage;
+  o->momentum_buffer = ctx->mom; o->momentum_ready = &ctx->ds->mom_ready;
   return 0;
 }
 
@@ -546,7 +552,8 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   mark();
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->host_mail, c->bnbuf, c->nbt, c->ds, c->comm, B,
-              rows_c1, gw_rows, planes ? ns2p : ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval};
+              rows_c1, gw_rows, planes ? ns2p : ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval,
+              c->mom, cfg.momentum, cfg.weight_decay, cfg.dampening, cfg.nesterov};
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();
   return cudaGetLastError();

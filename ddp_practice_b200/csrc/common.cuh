@@ -98,6 +98,7 @@ struct DevState {
   int growth_tracker;
   float found_inf;
   float loss;
+  int mom_ready;                  // SGD momentum buffers hold values (set by the first executed step)
 };
 
 // global BN statistics of the current step, written by the bn_relu_pool kernel

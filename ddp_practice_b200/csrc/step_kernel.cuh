@@ -40,6 +40,10 @@ struct StepArgs {
   int use_scaler, sync;
   float lr, growth_factor, backoff_factor;
   int growth_interval;
+  // the other torch.optim.SGD knobs (sgd.py:425-465); all zero for the reference
+  float* mom;  // [N_PAD] momentum buffers
+  float momentum, weight_decay, dampening;
+  int nesterov;
 };
 
 // conv2's filter is kept, besides its fp32 master copy, as ready-made tcgen05 B operands
@@ -84,6 +88,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   const unsigned long long epoch = a.ds->epoch;
   const float scale = a.ds->scale;
   const int tracker = a.ds->growth_tracker;
+  const int mom_ready = a.ds->mom_ready;
   if (tid == 0) s_nonfinite = 0;
   // parameters are fetched now, long before they are needed, so the load overlaps everything below
   float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -253,6 +258,29 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   // ---- 5. SGD (skipped on overflow), same expression as _foreach_add_(p, g, alpha=-lr)
   if (valid && !found) {
     float4 p = p4;
+    if (a.weight_decay != 0.f) {  // _foreach_add(grads, params, alpha=weight_decay): a new tensor, .grad stays as it was
+      u.x = fmaf(a.weight_decay, p.x, u.x); u.y = fmaf(a.weight_decay, p.y, u.y);
+      u.z = fmaf(a.weight_decay, p.z, u.z); u.w = fmaf(a.weight_decay, p.w, u.w);
+    }
+    if (a.momentum != 0.f) {
+      float4 b = u;  // first executed step: buf = clone(grad)
+      if (mom_ready) {  // _foreach_mul_(bufs, momentum); _foreach_add_(bufs, grads, alpha=1 - dampening)
+        b = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (e + 4 <= N_PARAM) b = *reinterpret_cast<const float4*>(a.mom + e);
+        else { b.x = a.mom[e]; b.y = a.mom[e + 1]; }
+        const float k = 1.0f - a.dampening;
+        b.x = fmaf(k, u.x, b.x * a.momentum); b.y = fmaf(k, u.y, b.y * a.momentum);
+        b.z = fmaf(k, u.z, b.z * a.momentum); b.w = fmaf(k, u.w, b.w * a.momentum);
+      }
+      if (e + 4 <= N_PARAM) *reinterpret_cast<float4*>(a.mom + e) = b;
+      else { a.mom[e] = b.x; a.mom[e + 1] = b.y; }
+      if (a.nesterov) {  // _foreach_add_(grads, bufs, alpha=momentum)
+        u.x = fmaf(a.momentum, b.x, u.x); u.y = fmaf(a.momentum, b.y, u.y);
+        u.z = fmaf(a.momentum, b.z, u.z); u.w = fmaf(a.momentum, b.w, u.w);
+      } else {
+        u = b;
+      }
+    }
     p.x = fmaf(-a.lr, u.x, p.x); p.y = fmaf(-a.lr, u.y, p.y);
     p.z = fmaf(-a.lr, u.z, p.z); p.w = fmaf(-a.lr, u.w, p.w);
     if (e + 4 <= N_PARAM) {
@@ -285,6 +313,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
           }
         }
       }
+      if (!found && a.momentum != 0.f) a.ds->mom_ready = 1;
       a.ds->epoch = epoch + 1ull;
       if (a.host_mail != nullptr) {
         a.host_mail[0] = rnd<T>(s / (float)a.B);

@@ -38,7 +38,8 @@ class Engine:
     def __init__(self, dtype: str = "fp16", batch_cap: int = 32, rank: int = 0, world: int = 1,
                  device: Optional[int] = None, use_scaler: Optional[bool] = None, sync_bn: bool = True,
                  use_graph: bool = True, lr: float = 1e-4, init_scale: float = 65536.0, growth_factor: float = 2.0,
-                 backoff_factor: float = 0.5, growth_interval: int = 2000, conv_bias_double_round: bool = True):
+                 backoff_factor: float = 0.5, growth_interval: int = 2000, conv_bias_double_round: bool = True,
+                 momentum: float = 0.0, weight_decay: float = 0.0, dampening: float = 0.0, nesterov: bool = False):
         if not torch.cuda.is_available():
             raise NativeError("ddp_practice_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
         self.lib = _lib.load()
@@ -53,6 +54,7 @@ class Engine:
         cfg.conv_bias_double_round = int(conv_bias_double_round)
         cfg.lr, cfg.init_scale = lr, init_scale
         cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval = growth_factor, backoff_factor, growth_interval
+        cfg.momentum, cfg.weight_decay, cfg.dampening, cfg.nesterov = momentum, weight_decay, dampening, int(nesterov)
         self.cfg = cfg
         self.rank, self.world, self.batch_cap = rank, world, batch_cap
         ctx = C.c_void_p()
@@ -80,6 +82,8 @@ class Engine:
         self.counts = view(p.counts, (2,), "<f4")
         self.input_stage = view(p.input_stage, (batch_cap, 1, 28, 28), "<f4")
         self.label_stage = view(p.label_stage, (batch_cap,), "<i8")
+        self.momentum_buffer = view(p.momentum_buffer, (N_PARAMS,), "<f4")  # optimizer.state[p]['momentum_buffer'], flat
+        self.momentum_ready = view(p.momentum_ready, (1,), "<i4")           # 1 once a step has created them
         if dtype == "fp32":
             self.logits = view(p.logits, (batch_cap, 10), "<f4")
         else:

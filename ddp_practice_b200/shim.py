@@ -128,6 +128,7 @@ class DistributedDataParallel(_tnn.Module):
         self._engine_key = None
         self._armed = None
         self._steps = 0
+        self._mom_published = False  # optimizer.state[p]['momentum_buffer'] views handed out
         self.last_logits = None
 
     # -- construction helpers -------------------------------------------------------------
@@ -150,8 +151,9 @@ class DistributedDataParallel(_tnn.Module):
         sd_b = dict(self.module.named_buffers())
         return sd_p, sd_b
 
-    def _ensure_engine(self, use_scaler: bool, lr: float = 1e-4, scaler: "GradScaler" = None):
-        key = (use_scaler, float(lr))
+    def _ensure_engine(self, use_scaler: bool, lr: float = 1e-4, scaler: "GradScaler" = None, sgd: dict = None):
+        sgd = sgd or {}
+        key = (use_scaler, float(lr), tuple(sorted(sgd.items())))
         if self.engine is not None and self._engine_key == key:
             return self.engine
         sd_p, sd_b = self._named()
@@ -163,12 +165,18 @@ class DistributedDataParallel(_tnn.Module):
             kw = dict(init_scale=scaler._init_scale_now(), growth_factor=scaler._growth_factor,
                       backoff_factor=scaler._backoff_factor, growth_interval=scaler._growth_interval)
         tracker = scaler._tracker_now() if scaler is not None else 0
+        mom = None
         if self.engine is not None:
+            if int(self.engine.momentum_ready.item()):  # a changed hyper-parameter rebuilds the context: keep the buffers
+                mom = self.engine.momentum_buffer.clone()
             self.engine.close()
         eng = Engine(dtype=self.amp_dtype, batch_cap=self.batch_cap, rank=self.rank, world=self.world,
-                     device=self.device_index, use_scaler=use_scaler, sync_bn=self.sync_bn, lr=lr, **kw)
+                     device=self.device_index, use_scaler=use_scaler, sync_bn=self.sync_bn, lr=lr, **kw, **sgd)
         eng.connect()
         eng.load_state(flat.numpy(), bn.numpy(), nbt)
+        if mom is not None:
+            eng.momentum_buffer.copy_(mom)
+            eng.momentum_ready.fill_(1)
         if scaler is not None and tracker:
             eng.set_scaler(kw["init_scale"], tracker)
         # re-point the module's tensors at the library's memory: state_dict(), parameters(),
@@ -208,18 +216,48 @@ class DistributedDataParallel(_tnn.Module):
     def _arm(self, loss: _Loss, scaled: bool):
         self._armed = (loss, scaled)
 
-    def _run_step(self, use_scaler: bool, lr: float, scaler=None):
+    def _sync_momentum(self, optimizer, before: bool):
+        """`optimizer.state[p]['momentum_buffer']` are views of the library's flat buffer.  Before a step: adopt
+        buffers that came from `optimizer.load_state_dict`; after the first executed step: publish the views."""
+        eng = self.engine
+        sd_p, _ = self._named()
+        for name, _shape in _SPECS:
+            p = sd_p[name]
+            off, n, shape = p._b200_slice
+            view = eng.momentum_buffer[off:off + n].view(shape)
+            buf = optimizer.state.get(p, {}).get("momentum_buffer")
+            if before:
+                if buf is not None and buf.data_ptr() != view.data_ptr():
+                    view.copy_(buf.to(view.device, torch.float32))
+                    eng.momentum_ready.fill_(1)
+                    optimizer.state[p]["momentum_buffer"] = view
+            elif buf is None and int(eng.momentum_ready.item()):
+                optimizer.state[p]["momentum_buffer"] = view
+
+    def _run_step(self, use_scaler: bool, lr: float, scaler=None, sgd: dict = None, optimizer=None):
         if self._armed is None:
             raise RuntimeError("step() without a preceding loss.backward() / scaler.scale(loss).backward()")
         loss, scaled = self._armed
         if scaled != use_scaler:
             raise RuntimeError("scaler.scale(loss).backward() must be followed by scaler.step(optimizer), and "
                                "loss.backward() by optimizer.step()")
-        eng = self._ensure_engine(use_scaler, lr, scaler)
+        eng = self._ensure_engine(use_scaler, lr, scaler, sgd)
+        momentum = bool(sgd and sgd.get("momentum", 0.0) != 0.0 and optimizer is not None)
+        if momentum and optimizer.state:
+            # cheap sentinel: only a load_state_dict() since the last step makes the first buffer something else
+            # than our view of the library's memory
+            p0 = optimizer.param_groups[0]["params"][0]
+            b0 = optimizer.state.get(p0, {}).get("momentum_buffer")
+            if b0 is not None and b0.data_ptr() != eng.momentum_buffer.data_ptr():
+                self._sync_momentum(optimizer, before=True)
+                self._mom_published = True
         labels = loss.labels.contiguous()
         if labels.dtype != torch.int64:
             labels = labels.long()
         eng.train_step(loss.images, labels)
+        if momentum and not self._mom_published and int(eng.momentum_ready.item()):
+            self._sync_momentum(optimizer, before=False)
+            self._mom_published = True
         self._armed = None
         self._steps += 1
         loss.step_id = self._steps
@@ -293,14 +331,13 @@ class GradScaler:
     def step(self, optimizer):
         params = optimizer.param_groups[0]["params"]
         g = optimizer.param_groups[0]
-        if len(optimizer.param_groups) != 1 or g.get("momentum", 0) != 0 or g.get("weight_decay", 0) != 0 \
-                or g.get("nesterov", False) or g.get("dampening", 0) != 0 or g.get("maximize", False):
-            raise NotImplementedError("the fused step implements SGD(params, lr) with momentum 0 and weight_decay 0")
+        if len(optimizer.param_groups) != 1 or g.get("maximize", False):
+            raise NotImplementedError("the fused step implements torch.optim.SGD with one parameter group, maximize=False")
         owner = getattr(params[0], "_b200_owner", None)
         if owner is None:  # engine not built yet: find the wrapper through the armed loss
             owner = _find_owner(params)
         self._owner = owner
-        owner._run_step(True, float(g["lr"]), self)
+        owner._run_step(True, float(g["lr"]), self, _sgd_knobs(g), optimizer)
         self._loaded = None
 
     def update(self, new_scale=None):
@@ -323,6 +360,12 @@ class GradScaler:
             e.set_scaler(float(sd["scale"]), int(sd["_growth_tracker"]))
         else:
             self._loaded = dict(sd)
+
+
+def _sgd_knobs(g) -> dict:
+    """momentum / weight_decay / dampening / nesterov of a torch.optim.SGD param group (sgd.py:425-465)."""
+    return dict(momentum=float(g.get("momentum", 0.0)), weight_decay=float(g.get("weight_decay", 0.0)),
+                dampening=float(g.get("dampening", 0.0)), nesterov=bool(g.get("nesterov", False)))
 
 
 _OWNERS = []  # wrappers alive in this process, to route an optimizer to its wrapper before the engine exists
@@ -357,7 +400,7 @@ class SGD(torch.optim.SGD):
     def step(self, closure=None):
         g = self.param_groups[0]
         owner = getattr(g["params"][0], "_b200_owner", None) or _find_owner(g["params"])
-        owner._run_step(False, float(g["lr"]))
+        owner._run_step(False, float(g["lr"]), None, _sgd_knobs(g), self)
 
 
 class _NN(types.ModuleType):

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define DDPSTEP_ABI_VERSION 1
+#define DDPSTEP_ABI_VERSION 2
 
 #define DDPSTEP_N_PARAMS 29034   /* flat fp32 parameter / gradient bucket length   */
 #define DDPSTEP_N_BNBUF 96       /* rm1[16] rv1[16] rm2[32] rv2[32]                */
@@ -57,6 +57,13 @@ typedef struct ddpstep_config {
   float init_scale, growth_factor, backoff_factor; /* GradScaler()  grad_scaler.py:126-128   */
   int32_t growth_interval; /*                                       grad_scaler.py:129       */
   float bn_momentum, bn_eps; /* nn.BatchNorm2d defaults             ddp_main.py:18,24        */
+  /* The other knobs of torch.optim.SGD (torch/optim/sgd.py:425-465, the multi-tensor form):
+   * g += weight_decay * p; buf = g on the first executed step, else buf = momentum * buf +
+   * (1 - dampening) * g; g = nesterov ? g + momentum * buf : buf; p -= lr * g.  All zero
+   * (the reference, ddp_main.py:125) leaves the plain update.  A step skipped by the scaler
+   * touches neither p nor buf.  SURVEY.md section 8(f) N3.                                  */
+  float momentum, weight_decay, dampening;
+  int32_t nesterov;        /* needs momentum > 0 and dampening == 0, as in torch             */
 } ddpstep_config;
 
 /* Device pointers into the context's state, for zero-copy views (torch tensors that alias
@@ -75,6 +82,8 @@ typedef struct ddpstep_ptrs {
   float* counts;           /* [2] correct, size accumulators of test()       ddp_main.py:99-107 */
   float* input_stage;      /* [batch_cap,784] fp32 staging buffer for images                   */
   int64_t* label_stage;    /* [batch_cap] staging buffer for labels                            */
+  float* momentum_buffer;  /* [29034] SGD momentum buffers (optimizer.state[p]['momentum_buffer']) */
+  int32_t* momentum_ready; /* [1] 1 once a step has initialised them (torch creates them lazily) */
 } ddpstep_ptrs;
 
 /* Fill a config with the reference's defaults (fp16 autocast, GradScaler(), lr 1e-4). */

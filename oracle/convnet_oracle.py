@@ -76,6 +76,8 @@ class OracleState:
     growth_factor: float = 2.0
     backoff_factor: float = 0.5
     growth_interval: int = 2000
+    # torch.optim.SGD state (sgd.py:425-465): flat momentum buffer, created by the first executed step
+    momentum_buffer: Optional[torch.Tensor] = None
 
     @staticmethod
     def from_state_dict(sd: Dict[str, torch.Tensor]) -> "OracleState":
@@ -99,6 +101,7 @@ class OracleState:
             scale=self.scale, growth_tracker=self.growth_tracker,
             growth_factor=self.growth_factor, backoff_factor=self.backoff_factor,
             growth_interval=self.growth_interval,
+            momentum_buffer=None if self.momentum_buffer is None else self.momentum_buffer.clone(),
         )
 
 
@@ -300,7 +303,8 @@ class StepResult:
 
 
 def train_step(st: OracleState, xs: Sequence[torch.Tensor], ys: Sequence[torch.Tensor], dtype: str = "fp16",
-               use_scaler: bool = True, sync_bn: bool = True, lr: float = 1e-4) -> StepResult:
+               use_scaler: bool = True, sync_bn: bool = True, lr: float = 1e-4, momentum: float = 0.0,
+               weight_decay: float = 0.0, dampening: float = 0.0, nesterov: bool = False) -> StepResult:
     """One `train()` iteration on W = len(xs) ranks that share `st` (replicas are
     identical, as DDP guarantees).  Mutates `st` like the reference mutates model,
     optimizer and scaler.  With W > 1, `sync_bn=True` is the reference behaviour
@@ -360,10 +364,22 @@ def train_step(st: OracleState, xs: Sequence[torch.Tensor], ys: Sequence[torch.T
     else:
         found_inf = 0.0
     if found_inf == 0.0:
+        upd = avg
+        if momentum != 0.0 or weight_decay != 0.0:
+            # the other SGD knobs, op for op as `_single_tensor_sgd` / `_multi_tensor_sgd` (sgd.py:330-465); a step the
+            # scaler skips touches neither the parameters nor the buffer, and `.grad` (tap T-c) stays as it was
+            flat = st.flat_params()
+            upd = avg.add(flat, alpha=weight_decay) if weight_decay != 0.0 else avg.clone()
+            if momentum != 0.0:
+                if st.momentum_buffer is None:
+                    st.momentum_buffer = upd.clone()
+                else:
+                    st.momentum_buffer.mul_(momentum).add_(upd, alpha=1.0 - dampening)
+                upd = upd.add(st.momentum_buffer, alpha=momentum) if nesterov else st.momentum_buffer
         off = 0
         for name, shape in PARAM_SPECS:
             n = math.prod(shape)
-            p[name] = p[name] + torch.tensor(-lr, dtype=torch.float32) * avg[off:off + n].view(shape)
+            p[name] = p[name] + torch.tensor(-lr, dtype=torch.float32) * upd[off:off + n].view(shape)
             off += n
     if use_scaler:
         st.scale, st.growth_tracker = amp_update_scale(st.scale, st.growth_tracker, found_inf, st.growth_factor,

@@ -16,6 +16,9 @@ pinned on outputs of the reference itself:
   ddp_gloo_w2.npz   ddp_main.ConvNet (plain BN, fp32) under real 2-process gloo
                     DistributedDataParallel: averaged grads, params, rank-0 buffers.
   test_counts.npz   the body of origin_main.test() on 96 images in 3 batches.
+  origin_fp32_nesterov.npz / amp_fp16_momentum.npz
+                    the same two loops with SGD(momentum, weight_decay, dampening / nesterov)
+                    (`python tests/golden/make_golden.py sgd` writes only these).
 """
 import contextlib
 import importlib.util
@@ -57,12 +60,17 @@ def flat_grads(model):
     return torch.cat([named[n].grad.reshape(-1) for n, _ in PARAM_SPECS]).numpy().copy()
 
 
-def gen_origin(path, batch, steps, seed=3407):
+def sgd_arrays(kw):
+    return {"sgd_" + k: np.float64(kw.get(k, d)) for k, d in
+            (("lr", 1e-4), ("momentum", 0.0), ("weight_decay", 0.0), ("dampening", 0.0), ("nesterov", 0.0))}
+
+
+def gen_origin(path, batch, steps, seed=3407, **sgd_kw):
     ref = load_ref("origin_main")
     torch.manual_seed(seed)
     model = ref.ConvNet()
     criterion = nn.CrossEntropyLoss()
-    optimizer = torch.optim.SGD(model.parameters(), 1e-4)
+    optimizer = torch.optim.SGD(model.parameters(), **{"lr": 1e-4, **sgd_kw})
     x, y = synthetic_mnist(batch * steps)
     out = sd_arrays(model, "init_")
     out["x"], out["y"] = x.numpy(), y.numpy()
@@ -80,11 +88,12 @@ def gen_origin(path, batch, steps, seed=3407):
     out["losses"] = np.array(losses, dtype=np.float64)
     out["grads"] = np.stack(grads)
     out.update(sd_arrays(model, "final_"))
+    out.update(sgd_arrays(sgd_kw))
     out["batch"], out["steps"] = np.int64(batch), np.int64(steps)
     np.savez_compressed(path, **out)
 
 
-def gen_amp(path, dtype, batch=8, steps=4, seed=3407):
+def gen_amp(path, dtype, batch=8, steps=4, seed=3407, **sgd_kw):
     ref = load_ref("ddp_main")
     # the reference's forward opens `torch.cuda.amp.autocast()`; on a CPU-only host that
     # context disables itself, so point it at CPU autocast of the dtype under test
@@ -92,7 +101,7 @@ def gen_amp(path, dtype, batch=8, steps=4, seed=3407):
     torch.manual_seed(seed)
     model = ref.ConvNet()
     criterion = nn.CrossEntropyLoss()
-    optimizer = torch.optim.SGD(model.parameters(), 1e-4)
+    optimizer = torch.optim.SGD(model.parameters(), **{"lr": 1e-4, **sgd_kw})
     scaler = torch.amp.GradScaler("cpu")
     x, y = synthetic_mnist(batch * steps)
     out = sd_arrays(model, "init_")
@@ -121,6 +130,7 @@ def gen_amp(path, dtype, batch=8, steps=4, seed=3407):
     out["found_inf"] = np.array(founds, dtype=np.float64)
     out["grads"] = np.stack(grads)
     out.update(sd_arrays(model, "final_"))
+    out.update(sgd_arrays(sgd_kw))
     out["batch"], out["steps"] = np.int64(batch), np.int64(steps)
     np.savez_compressed(path, **out)
 
@@ -198,15 +208,28 @@ def gen_test_counts(path, seed=3407):
     np.savez_compressed(path, **out)
 
 
+def gen_sgd_knobs():
+    """the reference's model / loop body with the other torch.optim.SGD knobs switched on (the
+    reference itself only ever passes lr; the optimizer class is the same)."""
+    gen_origin(os.path.join(HERE, "origin_fp32_nesterov.npz"), batch=8, steps=4, lr=1e-2, momentum=0.9,
+               weight_decay=5e-4, nesterov=True)
+    gen_amp(os.path.join(HERE, "amp_fp16_momentum.npz"), torch.float16, steps=5, lr=1e-3, momentum=0.9,
+            dampening=0.1, weight_decay=1e-3)
+
+
 if __name__ == "__main__":
     torch.set_num_threads(1)
     torch.use_deterministic_algorithms(True)
+    if sys.argv[1:] == ["sgd"]:  # only the N3 vectors (leaves the others byte-identical)
+        gen_sgd_knobs()
+        raise SystemExit(0)
     gen_origin(os.path.join(HERE, "origin_fp32.npz"), batch=8, steps=3)
     gen_origin(os.path.join(HERE, "global_w4.npz"), batch=32, steps=2)
     gen_amp(os.path.join(HERE, "amp_fp16.npz"), torch.float16)
     gen_amp(os.path.join(HERE, "amp_bf16.npz"), torch.bfloat16)
     gen_test_counts(os.path.join(HERE, "test_counts.npz"))
     gen_gloo(os.path.join(HERE, "ddp_gloo_w2.npz"))
+    gen_sgd_knobs()
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

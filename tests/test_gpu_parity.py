@@ -322,3 +322,55 @@ def test_argument_errors_are_reported():
     with pytest.raises(NativeError):
         _engine(world=9)
     e.close()
+
+
+# ------------------------------------------------------------------ the other torch.optim.SGD knobs
+
+
+@pytest.mark.parametrize("dtype,kw", [
+    ("fp32", dict(lr=1e-2, momentum=0.9, weight_decay=5e-4, nesterov=True)),
+    ("fp16", dict(lr=1e-3, momentum=0.9, dampening=0.1, weight_decay=1e-3)),
+    ("fp16", dict(lr=1e-3, weight_decay=1e-2)),
+])
+def test_sgd_momentum_weight_decay_nesterov_match_torch_on_the_same_gradients(dtype, kw):
+    """The optimizer tail in isolation: feed torch.optim.SGD (CUDA, the multi-tensor path the reference would get)
+    the library's own unscaled gradients step by step; parameters and momentum buffers must agree BIT FOR BIT, and
+    a step the scaler skips must leave both untouched (torch creates the buffers lazily)."""
+    st = _seed_state()
+    e = _engine(dtype=dtype, batch_cap=32, use_scaler=dtype != "fp32", **kw)
+    e.load_state(st.flat_params().numpy(), _bn_of(st))
+    p_ref = torch.nn.Parameter(e.params.clone())
+    opt = torch.optim.SGD([p_ref], **kw)
+    x, y = O.synthetic_mnist(32 * 5)
+    for s in range(5):
+        before = e.params.clone()
+        e.train_step(x[s * 32:(s + 1) * 32].cuda().contiguous(), y[s * 32:(s + 1) * 32].cuda().contiguous())
+        torch.cuda.synchronize()
+        if e.found_inf.item() == 1.0:
+            assert torch.equal(e.params, before) and (s > 0 or e.momentum_ready.item() == 0)
+            continue
+        p_ref.grad = e.grads.clone()
+        opt.step()
+        assert torch.equal(e.params.view(torch.int32), p_ref.detach().view(torch.int32)), f"step {s}"
+        if kw.get("momentum"):
+            assert e.momentum_ready.item() == 1
+            assert torch.equal(e.momentum_buffer.view(torch.int32), opt.state[p_ref]["momentum_buffer"].view(torch.int32))
+    e.close()
+
+
+def test_sgd_momentum_trajectory_matches_oracle():
+    st = _seed_state()
+    kw = dict(lr=1e-3, momentum=0.9, dampening=0.1, weight_decay=1e-3)
+    e = _engine(dtype="fp16", batch_cap=32, **kw)
+    e.load_state(st.flat_params().numpy(), _bn_of(st))
+    x, y = O.synthetic_mnist(32 * 4)
+    ini = st.flat_params().clone()
+    for s in range(4):
+        xs, ys = x[s * 32:(s + 1) * 32], y[s * 32:(s + 1) * 32]
+        r = O.train_step(st, [xs], [ys], dtype="fp16", **kw)
+        e.train_step(xs.cuda().contiguous(), ys.cuda().contiguous())
+        torch.cuda.synchronize()
+        assert e.found_inf.item() == r.found_inf and e.scale.item() == st.scale
+    assert_grads_close(e.params.cpu() - ini, st.flat_params() - ini, 6e-2, "accumulated update")  # flips allowed
+    assert_grads_close(e.momentum_buffer.cpu(), st.momentum_buffer, 6e-2, "momentum buffer")
+    e.close()

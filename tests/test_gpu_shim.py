@@ -93,7 +93,7 @@ def test_shim_rejects_misuse():
     with pytest.raises(RuntimeError, match="backward"):
         GradScaler().step(opt)
     with pytest.raises(NotImplementedError):
-        GradScaler().step(torch.optim.SGD(model.parameters(), 1e-4, momentum=0.9))
+        GradScaler().step(torch.optim.SGD(model.parameters(), 1e-4, maximize=True))
 
 
 def test_checkpoint_save_load_resume_is_bit_exact(tmp_path):
@@ -133,3 +133,51 @@ def test_checkpoint_save_load_resume_is_bit_exact(tmp_path):
     # and the file loads into the plain torch model the reference would use
     ref = RefConvNet(torch.float16, "cuda")
     ref.load_state_dict({k.removeprefix("module."): v.cpu() for k, v in ck["model"].items()})
+
+
+def test_momentum_sgd_through_the_shim_and_optimizer_checkpoint_resume(tmp_path):
+    """SURVEY 8(f) N3 through the reference's call surface: SGD(momentum, weight_decay) handed to scaler.step();
+    `optimizer.state_dict()` carries the momentum buffers (views of the library's memory), and a run resumed from
+    {"model", "scaler", "optimizer"} continues bit for bit."""
+    from ddp_practice_b200.shim import GradScaler, nn
+    kw = dict(lr=1e-3, momentum=0.9, weight_decay=1e-3)
+
+    def build(seed):
+        torch.manual_seed(seed)
+        m = nn.parallel.DistributedDataParallel(
+            nn.SyncBatchNorm.convert_sync_batchnorm(RefConvNet(torch.float16, "cuda").cuda()), device_ids=[0])
+        return m, nn.CrossEntropyLoss().cuda(), torch.optim.SGD(m.parameters(), **kw), GradScaler()
+
+    x, y = O.synthetic_mnist(32 * 6)
+    batches = [(x[i * 32:(i + 1) * 32], y[i * 32:(i + 1) * 32]) for i in range(6)]
+    m0, c0, o0, s0 = build(3407)
+    _reference_style_loop(m0, batches, c0, o0, s0)
+    torch.cuda.synchronize()
+    bufs = [o0.state[p]["momentum_buffer"] for p in o0.param_groups[0]["params"]]
+    assert torch.equal(torch.cat([b.reshape(-1) for b in bufs]), m0.engine.momentum_buffer)
+    assert float(torch.cat([b.reshape(-1) for b in bufs]).abs().sum()) > 0
+    # same thing straight through the engine
+    from ddp_practice_b200 import Engine
+    torch.manual_seed(3407)
+    st = O.OracleState.from_state_dict(RefConvNet(torch.float16, "cuda").state_dict())
+    e = Engine(dtype="fp16", batch_cap=32, **kw)
+    bn = torch.cat([st.running_mean[0], st.running_var[0], st.running_mean[1], st.running_var[1]])
+    e.load_state(st.flat_params().numpy(), bn.numpy())
+    for xb, yb in batches:
+        e.train_step(xb.cuda().contiguous(), yb.cuda().contiguous())
+    torch.cuda.synchronize()
+    assert torch.equal(e.params.cpu(), flat_params(m0)) and torch.equal(e.momentum_buffer, m0.engine.momentum_buffer)
+    e.close()
+    # interrupted after 3 steps, resumed in fresh objects
+    m1, c1, o1, s1 = build(3407)
+    _reference_style_loop(m1, batches[:3], c1, o1, s1)
+    path = str(tmp_path / "ck.pt")
+    torch.save({"model": m1.state_dict(), "scaler": s1.state_dict(), "optimizer": o1.state_dict()}, path)
+    ck = torch.load(path)
+    assert len(ck["optimizer"]["state"]) == 10 and ck["optimizer"]["param_groups"][0]["momentum"] == 0.9
+    m2, c2, o2, s2 = build(1)
+    m2.load_state_dict(ck["model"]); s2.load_state_dict(ck["scaler"]); o2.load_state_dict(ck["optimizer"])
+    _reference_style_loop(m2, batches[3:], c2, o2, s2)
+    torch.cuda.synchronize()
+    assert torch.equal(flat_params(m2), flat_params(m0))
+    assert torch.equal(m2.engine.momentum_buffer, m0.engine.momentum_buffer)

@@ -164,3 +164,40 @@ def test_fp16_overflow_cycle_is_data_independent():
     whenever scale == 65536; bf16 represents it exactly."""
     assert not torch.isfinite(O.rnd(torch.tensor(65536.0), torch.float16))
     assert O.rnd(torch.tensor(65536.0), torch.bfloat16).item() == 65536.0
+
+
+# ------------------------------------------------------------------ SURVEY 8(f) N3: the other torch.optim.SGD knobs
+
+
+def _sgd_kw(g):
+    return dict(lr=float(g["sgd_lr"]), momentum=float(g["sgd_momentum"]), weight_decay=float(g["sgd_weight_decay"]),
+                dampening=float(g["sgd_dampening"]), nesterov=bool(g["sgd_nesterov"]))
+
+
+def test_origin_fp32_nesterov_weight_decay_matches_reference():
+    g = load_golden("origin_fp32_nesterov.npz")
+    kw = _sgd_kw(g)
+    assert kw["nesterov"] and kw["momentum"] == 0.9 and kw["weight_decay"] == 5e-4
+    st, ini = state_from_golden(g), state_from_golden(g)
+    for s, x, y in _steps(g):
+        r = O.train_step(st, [x], [y], dtype="fp32", use_scaler=False, **kw)
+        assert r.losses[0] == pytest.approx(g["losses"][s], rel=FP32_TOL)
+        assert_grads_close(r.grads, g["grads"][s], 2e-5, f"step {s}")  # .grad itself: weight decay must not leak in
+    fin = state_from_golden(g, "final_")
+    assert_grads_close(st.flat_params() - ini.flat_params(), fin.flat_params() - ini.flat_params(), 2e-5, "update")
+
+
+def test_amp_fp16_momentum_dampening_matches_reference():
+    g = load_golden("amp_fp16_momentum.npz")
+    kw = _sgd_kw(g)
+    assert kw["dampening"] == pytest.approx(0.1) and not kw["nesterov"]
+    st, ini = state_from_golden(g), state_from_golden(g)
+    for s, x, y in _steps(g):
+        r = O.train_step(st, [x], [y], dtype="fp16", use_scaler=True, **kw)
+        assert r.found_inf == g["found_inf"][s] and st.scale == g["scales"][s] and st.growth_tracker == g["trackers"][s]
+        if s == 0:  # the overflowing first step is skipped: no buffer may exist yet (torch creates it lazily)
+            assert r.found_inf == 1.0 and st.momentum_buffer is None
+        else:
+            assert_grads_close(r.grads, g["grads"][s], AMP_TOL, f"step {s}")
+    fin = state_from_golden(g, "final_")
+    assert_grads_close(st.flat_params() - ini.flat_params(), fin.flat_params() - ini.flat_params(), AMP_TOL, "update")
