@@ -416,7 +416,11 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   const int g1 = std::min(B, 296);
   // small grids: the BN kernels reduce the conv kernels' partial sums themselves (no last-CTA tail)
   const int tsplit = B <= 64 ? 2 : 1;  // tcgen05 conv2: one M-tile per CTA at small batch
-  const int defer1 = g1 <= 64 ? c->defer_stats : 0, defer2 = std::min(B, 296) <= 64 ? c->defer_stats : 0;
+  // conv2 on the tensor cores writes one partial row per (image CTA, M-tile): 2B rows at small batch.  The tagged-row
+  // scheme reads at most 64 rows; between 33 and 64 images the plain deferred scheme (any row count) takes over.
+  const int rows2 = std::min(B, 296) * ((!std::is_same<T, float>::value && c->use_tc) ? tsplit : 1);
+  const int defer1 = g1 <= 64 ? c->defer_stats : 0;
+  const int defer2 = std::min(B, 296) > 64 ? 0 : (rows2 <= 64 ? c->defer_stats : std::min(c->defer_stats, 1));
   Conv1Args a1{x, c->params, c->y1, defer1 == 2 ? c->part1_ll : c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps,
                tiles_in_conv1 ? c->w2_tiles : nullptr, g1};
   constexpr int kTileCtas = 25600 / (C1_GROUPS * C1_THREADS);  // 50 extra blockIdx.x values x 4 groups x 128 threads

@@ -89,13 +89,27 @@ def test_eval_counts_golden():
 def test_step_matches_oracle(dtype, batch):
     """Same seeds, same synthetic MNIST-shaped inputs; 4 steps.  Scaler decisions bit-exact,
     loss and gradients within the stated tolerance, every tapped activation compared."""
+    _check_steps_against_oracle(dtype, batch, 4, batch)
+
+
+@pytest.mark.parametrize("dtype,batch", [("fp16", 1), ("fp16", 2), ("fp16", 63), ("fp16", 64), ("fp16", 65), ("fp16", 130),
+                                         ("fp16", 300), ("bf16", 65), ("fp32", 1), ("fp32", 65)])
+def test_batch_size_boundaries_match_oracle(dtype, batch):
+    """Edges of the kernel selection: a single image, the last batch that uses the small-batch kernels (64: conv1 on
+    CUDA cores, tagged partial rows, fused tile refresh / BN2 pass 1), the first that does not (65: tcgen05 conv1,
+    last-CTA finalisation), more images than CTAs (300 > 296), all inside a larger batch_cap.  Step 0 overflows under
+    fp16 (scale 65536 in the loss dtype), steps 1-2 carry real gradients."""
+    _check_steps_against_oracle(dtype, batch, 3, 320)
+
+
+def _check_steps_against_oracle(dtype, batch, steps, batch_cap):
     st = _seed_state()
     amp = dtype != "fp32"
-    e = _engine(dtype=dtype, batch_cap=batch, use_scaler=amp)
+    e = _engine(dtype=dtype, batch_cap=batch_cap, use_scaler=amp)
     e.load_state(st.flat_params().numpy(), _bn_of(st))
-    x, y = O.synthetic_mnist(batch * 4)
+    x, y = O.synthetic_mnist(batch * steps)
     tol = AMP_TOL if amp else FP32_TOL
-    for s in range(4):
+    for s in range(steps):
         xs, ys = x[s * batch:(s + 1) * batch], y[s * batch:(s + 1) * batch]
         before = st.clone()
         r = O.train_step(st, [xs], [ys], dtype=dtype, use_scaler=amp)
