@@ -30,7 +30,7 @@ def main():
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
     amp = dtype != "fp32"
-    B = 32
+    B = int(sys.argv[3]) if len(sys.argv) > 3 else 32
     # the reference's construction sequence, ddp_main.py:117-126 (replicas start different: DDP broadcasts rank 0)
     torch.manual_seed(1000 + rank)
     model = RefConvNet(TDT[dtype], "cuda").cuda()
