@@ -107,10 +107,10 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       bool live;
-      const int arg = pool_winner<T>(v[u], mu, is, g, b, live);
+      float win;
+      pool_winner<T>(v[u], mu, is, g, b, live, win);
       if (live) {
         sdy += d[u];
-        const float win = arg == 0 ? v[u][0] : arg == 1 ? v[u][1] : arg == 2 ? v[u][2] : v[u][3];  // selects, not a dynamic index
         sdyx = fmaf(d[u], win - mu, sdyx);
       }
     }
@@ -123,10 +123,10 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
     load2<T>(src + H, v[2], v[3]);
     const float d = ldf<T>(&dp[((size_t)n * C + c) * HP * HP + w]);
     bool live;
-    const int arg = pool_winner<T>(v, mu, is, g, b, live);
+    float win;
+    pool_winner<T>(v, mu, is, g, b, live, win);
     if (live) {
       sdy += d;
-      const float win = arg == 0 ? v[0] : arg == 1 ? v[1] : arg == 2 ? v[2] : v[3];
       sdyx = fmaf(d, win - mu, sdyx);
     }
   }

@@ -240,6 +240,24 @@ __device__ __forceinline__ int pool_winner(const float y[4], float mu, float is,
   live = best > 0.f;
   return arg;
 }
+// Same, also handing back the winner's conv output (tracked with selects: indexing y[] by the run-time winner would
+// push the array into local memory, a chain of ?: over it compiles to branches).
+template <typename T>
+__device__ __forceinline__ int pool_winner(const float y[4], float mu, float is, float g, float b, bool& live, float& win) {
+  float best = -1.f;
+  int arg = 0;
+  win = y[0];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float r = fmaxf(rnd<T>((y[i] - mu) * is * g + b), 0.f);
+    const bool better = r > best;
+    best = better ? r : best;
+    arg = better ? i : arg;
+    win = better ? y[i] : win;
+  }
+  live = best > 0.f;
+  return arg;
+}
 
 // Optional in-kernel phase timestamps (build with -DDDPSTEP_TRACE): CTA 0 writes globaltimer values
 // into a small global buffer so latency chains inside a kernel can be read off directly.

@@ -724,7 +724,7 @@ struct FcArgs {
 // NI = images per loop iteration: 1 at small batch (shortest chain), 4 at large batch (the two block-wide
 // synchronisations per iteration are shared by four images and four times as many loads are in flight).
 template <typename T, int NI>
-__global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
+__global__ void __launch_bounds__(224, NI == 4 ? 2 : 1) k_fc_ce(FcArgs a) {  // NI = 4: two CTAs per SM, the 296-CTA grid is one wave
   if (threadIdx.x == 0) TRACE(5 * 16 + 0);
   __shared__ float red[7][NI][10];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -851,8 +851,8 @@ __global__ void __launch_bounds__(224) k_fc_ce(FcArgs a) {
           const int k = tid + 224 * i, c = k / 49;
           const float mu = s_bn[c][0];
           bool live;
-          const int arg = pool_winner<T>(yw[i], mu, s_bn[c][1], s_bn[c][2], s_bn[c][3], live);
-          const float win = arg == 0 ? yw[i][0] : arg == 1 ? yw[i][1] : arg == 2 ? yw[i][2] : yw[i][3];  // no dynamic index: registers
+          float win;
+          pool_winner<T>(yw[i], mu, s_bn[c][1], s_bn[c][2], s_bn[c][3], live, win);
           s_el[k] = live ? make_float2(df[i], df[i] * (win - mu)) : make_float2(0.f, 0.f);
         }
         __syncthreads();
