@@ -19,8 +19,9 @@ def _state():
     return st.flat_params().numpy(), bn
 
 
-@pytest.mark.parametrize("dtype", ["fp16", "fp32"])
-def test_indexed_uint8_step_equals_float_batch_step(dtype):
+@pytest.mark.parametrize("dtype,B", [("fp16", 32), ("fp32", 32), ("fp16", 96), ("bf16", 96)])
+def test_indexed_uint8_step_equals_float_batch_step(dtype, B):
+    """B = 96 takes the large-batch kernels (conv1 and its weight gradient on tcgen05 read the uint8 rows too)."""
     from ddp_practice_b200 import Engine
     g = torch.Generator().manual_seed(5)
     n = 1000  # not a multiple of 32: the last batch is ragged, like 7500 % 32 in the reference at W=8
@@ -31,17 +32,17 @@ def test_indexed_uint8_step_equals_float_batch_step(dtype):
     order = torch.tensor(list(iter(sampler)), dtype=torch.int64)
     assert len(order) == 500
     params, bn = _state()
-    a = Engine(dtype=dtype, batch_cap=32, use_scaler=dtype != "fp32")
-    b = Engine(dtype=dtype, batch_cap=32, use_scaler=dtype != "fp32")
+    a = Engine(dtype=dtype, batch_cap=B, use_scaler=dtype != "fp32")
+    b = Engine(dtype=dtype, batch_cap=B, use_scaler=dtype != "fp32")
     for e in (a, b):
         e.load_state(params, bn)
     img_d, lab_d, ord_d = images.cuda(), labels.cuda(), order.cuda()
-    for lo in range(0, 500, 32):
-        idx = ord_d[lo:lo + 32].contiguous()
+    for lo in range(0, 500, B):
+        idx = ord_d[lo:lo + B].contiguous()
         a.train_step_indexed(img_d, lab_d, idx)
         # what the reference's pipeline hands to train(): ToTensor (uint8 -> float / 255), batch, .cuda()
-        xb = (images[order[lo:lo + 32]].float() / 255).cuda().contiguous()
-        yb = labels[order[lo:lo + 32]].cuda().contiguous()
+        xb = (images[order[lo:lo + B]].float() / 255).cuda().contiguous()
+        yb = labels[order[lo:lo + B]].cuda().contiguous()
         b.train_step(xb, yb)
         torch.cuda.synchronize()
         assert a.loss.item() == b.loss.item()
@@ -49,11 +50,11 @@ def test_indexed_uint8_step_equals_float_batch_step(dtype):
     assert torch.equal(a.grads.view(torch.int32), b.grads.view(torch.int32))
     # test(): counts over the same shard, ddp_main.py:101-107
     a.reset_counts(); b.reset_counts()
-    for lo in range(0, 500, 32):
-        idx = ord_d[lo:lo + 32].contiguous()
+    for lo in range(0, 500, B):
+        idx = ord_d[lo:lo + B].contiguous()
         la = a.eval_batch_indexed(img_d, lab_d, idx).clone()
-        xb = (images[order[lo:lo + 32]].float() / 255).cuda().contiguous()
-        lb = b.eval_batch(xb, labels[order[lo:lo + 32]].cuda().contiguous())
+        xb = (images[order[lo:lo + B]].float() / 255).cuda().contiguous()
+        lb = b.eval_batch(xb, labels[order[lo:lo + B]].cuda().contiguous())
         assert torch.equal(la, lb)
     assert a.read_counts() == b.read_counts() and a.read_counts()[1] == 500.0
     a.close(); b.close()

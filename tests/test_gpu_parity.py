@@ -388,3 +388,22 @@ def test_sgd_momentum_trajectory_matches_oracle():
     assert_grads_close(e.params.cpu() - ini, st.flat_params() - ini, 6e-2, "accumulated update")  # flips allowed
     assert_grads_close(e.momentum_buffer.cpu(), st.momentum_buffer, 6e-2, "momentum buffer")
     e.close()
+
+
+@pytest.mark.parametrize("dtype,batch", [("fp16", 1), ("fp16", 64), ("fp16", 65), ("fp16", 300), ("fp32", 65)])
+def test_eval_batch_size_boundaries_match_oracle(dtype, batch):
+    """`model.eval()` forward (running statistics) at the edges of the kernel selection, against the oracle."""
+    st = _seed_state()
+    st.running_mean = [torch.randn(16) * 0.1, torch.randn(32) * 0.1]   # off their init values
+    st.running_var = [torch.rand(16) + 0.5, torch.rand(32) + 0.5]
+    e = _engine(dtype=dtype, batch_cap=320, use_scaler=dtype != "fp32")
+    e.load_state(st.flat_params().numpy(), _bn_of(st))
+    x, y = O.synthetic_mnist(batch, seed=17)
+    ref = O.eval_logits(st, x, dtype)
+    e.reset_counts()
+    got = e.eval_batch(x.cuda().contiguous(), y.cuda().contiguous()).float().cpu()
+    tol = 2e-2 if dtype != "fp32" else 1e-4
+    assert torch.allclose(got, ref.float(), rtol=tol, atol=tol * ref.float().abs().max().item())
+    c, s = e.read_counts()
+    assert s == float(batch) and c == float((got.argmax(1) == y).sum())
+    e.close()
