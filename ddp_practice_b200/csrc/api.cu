@@ -61,6 +61,7 @@ struct ddpstep_ctx {
   // small grids (<= 64 partial rows): 2 = tagged rows, the BN consumer's first CTA publishes the statistics before its grid
   // dependency resolves; 1 = plain rows, every consumer CTA reduces them; 0 = the producer's last CTA finalises (DDPSTEP_DEFER)
   int defer_stats = 2;
+  bool fuse_head = true;  // BN2 + ReLU + pool inside the Linear+CE kernel at small batch (DDPSTEP_HEAD=0: separate kernel)
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   // the same partial rows as tagged 8-byte words (store_partial), one buffer per producer so that a tag can never match
   // another stage's words of the same step
@@ -168,6 +169,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
     ctx->use_pdl = !(envp && envp[0] == '0');
     const char* envd = getenv("DDPSTEP_DEFER");
     if (envd && envd[0] >= '0' && envd[0] <= '2') ctx->defer_stats = envd[0] - '0';
+    const char* envh = getenv("DDPSTEP_HEAD");
+    ctx->fuse_head = !(envh && envh[0] == '0');
     const char* envw = getenv("DDPSTEP_WGRAD_TC");
     ctx->use_wgrad_tc = ctx->use_tc && !(envw && envw[0] == '0');
   }
@@ -470,12 +473,15 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   // 4. BN2 + ReLU + pool
   BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, st2, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 0, sync, cfg.bn_momentum, cfg.bn_eps,
                 defer2 == 2 ? c->part2_ll : defer2 ? c->part2 : nullptr, tc ? g2 * tsplit : g2, defer2 == 2};
-  launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark();
-  // 5. Linear + CE + dlogits + d(pool2 out)
-  // small batch: BN2's backward pass 1 rides in this kernel (one image per CTA, one tagged partial row per image)
+  // small batch: BN2's backward pass 1 rides in the Linear+CE kernel (one image per CTA, one tagged partial row per
+  // image), and so does BN2 + ReLU + pool itself when conv2 left tagged rows (`head`: slot 4 stays empty)
   const bool fuse_bn2r = c->defer_stats == 2 && B <= 64;
+  const bool head = fuse_bn2r && defer2 == 2 && c->fuse_head;
+  if (!head) { launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark(); }
+  else skip_slot();
+  // 5. Linear + CE + dlogits + d(pool2 out)
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, c->dlogits, c->dflat, c->nll, c->counts,
-           c->ds, B, cfg.use_scaler, 0, c->y2, st2, fuse_bn2r ? c->bpart2_ll : nullptr};
+           c->ds, B, cfg.use_scaler, 0, c->y2, st2, fuse_bn2r ? c->bpart2_ll : nullptr, b2, head ? 1 : 0};
   if (rec) rec->a_fc = f;
   if (B > 1184) launch_k(k_fc_ce<T, 4>, dim3(296), dim3(224), 0, s, f, pdl);
   else launch_k(k_fc_ce<T, 1>, dim3(std::min(B, 296)), dim3(224), 0, s, f, pdl);
@@ -610,7 +616,7 @@ static cudaError_t enqueue_eval(ddpstep_ctx* c, const BatchSrc& x, const int64_t
   BnPoolArgs b2{c->y2, c->p2, nullptr, c->params, c->st + 1, c->bnbuf, c->nbt, c->ds, c->comm, B, 1, 1, 0, cfg.bn_momentum, cfg.bn_eps, nullptr, 0};
   k_bn_relu_pool<T, 32, 14><<<clampi(cdiv(B * 32 * 49, 256), 1, 1184), 256, 0, s>>>(b2); mark();
   FcArgs f{c->p2, c->params, reinterpret_cast<const long long*>(y), x.idx, c->logits, nullptr, nullptr, nullptr, c->counts, c->ds, B, 0, 1,
-           nullptr, nullptr, nullptr};
+           nullptr, nullptr, nullptr, BnPoolArgs{}, 0};
   if (rec) rec->a_fc = f;
   if (B > 1184) k_fc_ce<T, 4><<<296, 224, 0, s>>>(f);
   else k_fc_ce<T, 1><<<std::min(B, 296), 224, 0, s>>>(f);

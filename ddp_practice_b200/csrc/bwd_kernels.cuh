@@ -178,9 +178,9 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, A
   const int c = threadIdx.x;
   const bool xchg = a.sync && a.comm.world > 1;
   const bool first = blockIdx.x == 0 && blockIdx.y == 0;
-  // issued first so that their latency hides behind the partial-sum loads below
+  // The forward statistics may have been written by the DIRECT predecessor (BN2 inside the Linear+CE kernel): they
+  // are read only after the grid dependency resolved, together with the polls.
   float n_tot = 0.f, inv_c = 0.f;
-  if (c < C) { n_tot = a.st->n_total; inv_c = a.st->invstd[c]; }
   const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
   // this rank's sums from the pass-1 partials: thread = (quarter of the rows, channel, which sum), so the
   // loads overlap; quarters are combined in fixed order.  CTA (0,0) also publishes d(gamma), d(beta) and
@@ -224,8 +224,6 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, A
   };
   auto publish = [&](bool self_too) {
     if (c < C) {
-      a.gdirect[OFF_G + c] = s_loc[C + c] * inv_c;  // d(gamma), local: DDP averages it
-      a.gdirect[OFF_BE + c] = s_loc[c];             // d(beta)
       for (int q = 0; q < a.comm.world; ++q) {  // the all_reduce of _functions.py:159 as pushed tagged words
         if (q == a.comm.rank ? !self_too : !xchg) continue;
         llword* slot = a.comm.peer[q]->ll_bn_bwd[a.layer][a.comm.rank];
@@ -241,9 +239,14 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, A
   }
   pdl_sync();  // predecessor: pass 1 (bpart)
   after_wait();
+  if (c < C) { n_tot = a.st->n_total; inv_c = a.st->invstd[c]; }
   if (a.defer == 1) {
     local_sums(false);
     if (first) publish(xchg);
+  }
+  if (first && a.defer != 0 && c < C) {  // this rank's d(gamma), d(beta): DDP averages them (s_loc: CTA (0,0)'s sums)
+    a.gdirect[OFF_G + c] = s_loc[C + c] * inv_c;
+    a.gdirect[OFF_BE + c] = s_loc[c];
   }
   if (c < C) {
     float s0, s1;
@@ -296,11 +299,12 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
   const T* __restrict__ dp = reinterpret_cast<const T*>(a.dpool);
   T* __restrict__ dy = reinterpret_cast<T*>(a.dy);
   const int total = max(0, n1 - n0) * HP * HP;
-  // The conv output and the BN statistics of this thread's first window are older than the predecessor's
-  // predecessor (a kernel is only launched once every CTA of the one before it has passed ITS wait), so they are
-  // fetched before the wait inside bn_backward_sums; the incoming gradient may come from the direct predecessor
-  // (pass 1 fused into the Linear/CE kernel) and is fetched right after the wait, together with the polls
-  const float mu = a.st->mean[c], is = a.st->invstd[c], g = a.params[OFF_G2 + c], b = a.params[OFF_BE2 + c];
+  // The conv output of this thread's first window is older than the predecessor's predecessor (a kernel is only
+  // launched once every CTA of the one before it has passed ITS wait), so it is fetched before the wait inside
+  // bn_backward_sums; the incoming gradient and BN2's statistics may come from the direct predecessor (pass 1 and
+  // BN2 itself fused into the Linear+CE kernel) and are fetched right after the wait, together with the polls
+  const float g = a.params[OFF_G2 + c], b = a.params[OFF_BE2 + c];
+  float mu = 0.f, is = 1.f;  // BN2's statistics may come from the direct predecessor too: fetched after the wait
   float pv[4] = {0.f, 0.f, 0.f, 0.f}, pd = 0.f;
   if (tid < total) {
     const int n = n0 + tid / (HP * HP), w = tid % (HP * HP), ph = w / HP, pw = w % HP;
@@ -309,6 +313,8 @@ __global__ void __launch_bounds__(256) k_bn2_bwd_apply(BnBwdArgs a) {
     load2<T>(y + off + H, pv[2], pv[3]);
   }
   bn_backward_sums<C>(a, s_k1, s_k2, [&] {
+    mu = a.st->mean[c];
+    is = a.st->invstd[c];
     if (tid < total) pd = ldf<T>(&dp[((size_t)(n0 + tid / (HP * HP)) * C + c) * HP * HP + tid % (HP * HP)]);
   });
   if (threadIdx.x == 0) TRACE(9 * 16 + 1);

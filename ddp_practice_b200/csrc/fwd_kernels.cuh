@@ -284,7 +284,7 @@ struct BnPoolArgs {
 // Local statistics from the producer's partial rows (column = (channel, stat), several row lanes per column, sums in
 // double, divisions / square root in fp32 as batch_norm_stats does).  Called by every thread of a 256-thread CTA.
 // LL = true: the rows are tagged words that are polled until they carry this step's tag.
-template <int C, bool LL>
+template <int C, bool LL, int BLOCK = 256>
 __device__ void bn_local_stats(const BnPoolArgs& a, float local_count, unsigned int tag, float& lmean, float& linvstd,
                                float& lvar_unb) {
   __shared__ double fin[512];
@@ -295,7 +295,7 @@ __device__ void bn_local_stats(const BnPoolArgs& a, float local_count, unsigned 
   if (lane < lanes) {
     // deferred mode means at most 64 rows: every load of this thread is issued before the first one is
     // consumed (ONE trip to L2 instead of rows / lanes / 4 of them); the sum keeps its row order
-    constexpr int NV = 64 / (256 / COLS);
+    constexpr int NV = (64 + BLOCK / COLS - 1) / (BLOCK / COLS);
     float v[NV];
     if (LL) {
       const llword* rows = reinterpret_cast<const llword*>(a.part);
@@ -374,22 +374,22 @@ struct BnOwn {
   long long nbt_old = 0;
 };
 
-template <int C>
+template <int C, int BLOCK = 256>
 __device__ void bn_forward_publish(const BnPoolArgs& a, float local_count, BnOwn& own) {
   const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
-  bn_local_stats<C, true>(a, local_count, tag, own.lmean, own.linvstd, own.lvar_unb);
+  bn_local_stats<C, true, BLOCK>(a, local_count, tag, own.lmean, own.linvstd, own.lvar_unb);
   if (threadIdx.x < C) bn_push_stats<C>(a, threadIdx.x, own.lmean, own.linvstd, own.lvar_unb, local_count, tag, true);
   own.have = true;
 }
 
 // CTA 0's early work: the old running statistics (the last kernel that wrote them belongs to the previous step) and,
 // with tagged rows, the publication of this rank's statistics.  Must be called by every thread of the CTA.
-template <int C>
+template <int C, int BLOCK = 256>
 __device__ __forceinline__ void bn_forward_early(const BnPoolArgs& a, int rm_off, int rv_off, float local_count, BnOwn& own) {
   if (blockIdx.x != 0 || a.eval) return;
   if (threadIdx.x < C) { own.rm_old = a.bnbuf[rm_off + threadIdx.x]; own.rv_old = a.bnbuf[rv_off + threadIdx.x]; }
   if (threadIdx.x == 0) own.nbt_old = a.nbt[a.layer];
-  if (a.ll) bn_forward_publish<C>(a, local_count, own);
+  if (a.ll) bn_forward_publish<C, BLOCK>(a, local_count, own);
 }
 
 template <int C>
@@ -719,6 +719,12 @@ struct FcArgs {
   const void* y2;       // conv2 output [B,32,14,14]
   const BnStat* st2;    // BN2 statistics of this step
   float* bpart2;
+  // ... and, when conv2 left tagged partial rows (`head`), BN2 + ReLU + pool as well: the pooling windows this kernel
+  // fetches for the backward pass ARE the seven features each thread feeds to the Linear layer, so the pooled tensor
+  // never makes a round trip through L2 and one kernel boundary disappears.  bn2.p receives p2 (the fc weight
+  // gradient reads it), CTA 0 plays the BN kernel's CTA 0 (publication, running statistics).
+  BnPoolArgs bn2;
+  int head;
 };
 
 // NI = images per loop iteration: 1 at small batch (shortest chain), 4 at large batch (the two block-wide
@@ -741,11 +747,11 @@ __global__ void __launch_bounds__(224, NI == 4 ? 2 : 1) k_fc_ce(FcArgs a) {  // 
   // fused BN2 backward pass 1: this thread's seven pooling windows of conv2's output (two launches old, so they may
   // be fetched before the wait)
   const bool fuse = NI == 1 && a.bpart2 != nullptr && (int)blockIdx.x < a.B;
+  const bool head = NI == 1 && a.head != 0;  // implies fuse; grid == B
   float yw[7][4];
   unsigned int ll_tag = 0u;
-  if (fuse) {
+  auto fetch_windows = [&]() {
     const T* __restrict__ y2 = reinterpret_cast<const T*>(a.y2);
-    ll_tag = (unsigned int)a.ds->epoch + 1u;
 #pragma unroll
     for (int i = 0; i < 7; ++i) {
       const int k = tid + 224 * i, c = k / 49, w = k % 49, ph = w / 7, pw = w % 7;
@@ -753,11 +759,35 @@ __global__ void __launch_bounds__(224, NI == 4 ? 2 : 1) k_fc_ce(FcArgs a) {  // 
       load2<T>(src, yw[i][0], yw[i][1]);
       load2<T>(src + 14, yw[i][2], yw[i][3]);
     }
-  }
-  pdl_sync();  // predecessor: BN2 + ReLU + pool (p2); the weights above do not depend on it
+  };
+  BnOwn own;
+  if (fuse) ll_tag = (unsigned int)a.ds->epoch + 1u;
+  if (head) bn_forward_early<32, 224>(a.bn2, BNB_RM2, BNB_RV2, (float)a.B * 196.f, own);  // CTA 0 publishes BN2's statistics
+  else if (fuse) fetch_windows();  // conv2's output is two launches old here
+  pdl_sync();  // predecessor: BN2 + ReLU + pool (p2), or conv2 itself (head); the weights above depend on neither
   if (threadIdx.x == 0) TRACE(5 * 16 + 1);
-  __shared__ float s_bn[32][4];  // BN2 mean, invstd, gamma, beta (the first two were written by the predecessor)
-  if (fuse && tid < 128) {
+  __shared__ float s_bn[32][4];  // BN2 mean, invstd, gamma, beta
+  float pooled[7];
+  if (head) {
+    __shared__ float s_mean2[32], s_invstd2[32];
+    fetch_windows();  // travels together with the poll for the published statistics
+    bn_forward_stats<32>(a.bn2, s_mean2, s_invstd2, BNB_RM2, BNB_RV2, (float)a.B * 196.f, own);
+    if (tid < 128) {
+      const int c = tid >> 2, q = tid & 3;
+      s_bn[c][q] = q == 0 ? s_mean2[c] : q == 1 ? s_invstd2[c] : q == 2 ? a.params[OFF_G2 + c] : a.params[OFF_BE2 + c];
+    }
+    __syncthreads();
+    T* __restrict__ p2w = reinterpret_cast<T*>(a.bn2.p);
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {  // BN2 + ReLU + 2x2 max-pool of this thread's seven windows = its seven fc inputs
+      const int k = tid + 224 * i, c = k / 49;
+      const float mu = s_bn[c][0], is = s_bn[c][1], gm = s_bn[c][2], bt = s_bn[c][3];
+      const float v0 = rnd<T>((yw[i][0] - mu) * is * gm + bt), v1 = rnd<T>((yw[i][1] - mu) * is * gm + bt);
+      const float v2 = rnd<T>((yw[i][2] - mu) * is * gm + bt), v3 = rnd<T>((yw[i][3] - mu) * is * gm + bt);
+      pooled[i] = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
+      stf<T>(&p2w[(size_t)blockIdx.x * 1568 + k], pooled[i]);
+    }
+  } else if (fuse && tid < 128) {  // the first two were written by the predecessor
     const int c = tid >> 2, q = tid & 3;
     s_bn[c][q] = q == 0 ? a.st2->mean[c] : q == 1 ? a.st2->invstd[c] : q == 2 ? a.params[OFF_G2 + c] : a.params[OFF_BE2 + c];
   }
@@ -771,7 +801,7 @@ __global__ void __launch_bounds__(224, NI == 4 ? 2 : 1) k_fc_ce(FcArgs a) {  // 
     for (int u = 0; u < NI; ++u)
 #pragma unroll
       for (int i = 0; i < 7; ++i)
-        xk[u][i] = (n0 + u < a.B) ? ldf<T>(&p2[(size_t)(n0 + u) * 1568 + tid + 224 * i]) : 0.f;
+        xk[u][i] = head ? pooled[i] : (n0 + u < a.B) ? ldf<T>(&p2[(size_t)(n0 + u) * 1568 + tid + 224 * i]) : 0.f;
 #pragma unroll
     for (int u = 0; u < NI; ++u)
 #pragma unroll

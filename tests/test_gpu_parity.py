@@ -284,7 +284,7 @@ def test_graph_replay_equals_eager_launches_and_is_deterministic():
             e.train_step(x[s * 32:(s + 1) * 32].cuda().contiguous(), y[s * 32:(s + 1) * 32].cuda().contiguous())
         torch.cuda.synchronize()
         outs.append((e.params.cpu().clone(), e.grads.cpu().clone(), e.bn_buffers.cpu().clone(), e.loss.item()))
-        assert e.launch_count() == 13 * 3  # at this batch the filter-tile refresh rides in conv1, BN2 backward pass 1 in Linear+CE
+        assert e.launch_count() == 12 * 3  # at this batch the filter-tile refresh rides in conv1, BN2 pool + backward pass 1 in Linear+CE
         e.close()
     for o in outs[1:]:
         assert torch.equal(o[0], outs[0][0]) and torch.equal(o[1], outs[0][1]) and torch.equal(o[2], outs[0][2])
