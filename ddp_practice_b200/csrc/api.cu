@@ -15,6 +15,7 @@
 #include "bwd_kernels.cuh"
 #include "conv2_tc.cuh"
 #include "conv1_tc.cuh"
+#include "bwd_mid_tc.cuh"
 #include "fwd_kernels.cuh"
 #include "step_kernel.cuh"
 
@@ -61,6 +62,10 @@ struct ddpstep_ctx {
   // small grids (<= 64 partial rows): 2 = tagged rows, the BN consumer's first CTA publishes the statistics before its grid
   // dependency resolves; 1 = plain rows, every consumer CTA reduces them; 0 = the producer's last CTA finalises (DDPSTEP_DEFER)
   int defer_stats = 2;
+  // BN2 backward apply + conv2 data gradient + BN1 backward pass 1 as one kernel (bwd_mid_tc.cuh).  Opt-in
+  // (DDPSTEP_MID=1): measured 47.0 vs 45.2 us per step -- the fused kernel itself saves ~4 us on the main chain, but the
+  // conv2 weight-gradient branch can then only start after it and becomes the critical path.
+  bool fuse_mid = false;
   bool fuse_head = true;  // BN2 + ReLU + pool inside the Linear+CE kernel at small batch (DDPSTEP_HEAD=0: separate kernel)
   float *nll = nullptr, *part1 = nullptr, *part2 = nullptr, *bpart = nullptr, *gpart = nullptr, *gdirect = nullptr;
   // the same partial rows as tagged 8-byte words (store_partial), one buffer per producer so that a tag can never match
@@ -169,6 +174,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
     ctx->use_pdl = !(envp && envp[0] == '0');
     const char* envd = getenv("DDPSTEP_DEFER");
     if (envd && envd[0] >= '0' && envd[0] <= '2') ctx->defer_stats = envd[0] - '0';
+    const char* envm = getenv("DDPSTEP_MID");
+    ctx->fuse_mid = envm && envm[0] == '1';
     const char* envh = getenv("DDPSTEP_HEAD");
     ctx->fuse_head = !(envh && envh[0] == '0');
     const char* envw = getenv("DDPSTEP_WGRAD_TC");
@@ -202,6 +209,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1W_TC_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1W_TC_SMEM);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bwd_mid_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, MID_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bwd_mid_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, MID_SMEM_BYTES);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1T_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1T_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
@@ -502,21 +511,32 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   r2p.per_split = cdiv(B, ns2p);
   if (!fuse_bn2r) { launch_k(k_bn_bwd_reduce<T, 32, 14>, dim3(32, ns2), dim3(256), 0, s, r2, pdl); mark(); }
   else skip_slot();
-  if (planes) {
+  // small batch on the tensor-core path: BN2 backward apply, the conv2 data gradient and BN1 backward pass 1 are one
+  // kernel per (image, M-tile) (bwd_mid_tc.cuh); slots 8 and 12 stay empty, slot 9 is the fused kernel
+  bool mid = false;
+  if constexpr (!std::is_same<T, float>::value) mid = c->use_tc && c->fuse_mid && fuse_bn2r && B <= 32;
+  if (mid) {
+    skip_slot();
+  } else if (planes) {
     if constexpr (!std::is_same<T, float>::value) launch_k(k_bn2_bwd_apply_planes<T>, dim3(4, ns2p), dim3(256), 0, s, r2p, pdl);
   } else {
     launch_k(k_bn2_bwd_apply<T>, dim3(32, ns2), dim3(256), 0, s, r2, pdl);
   }
-  mark();
+  if (!mid) mark();
   // 9. conv2 weight gradient partials, 10. conv2 data gradient
   const int gw = std::min(B, 37);
   Conv2WgradArgs w2{c->p1, c->dy2, c->gpart, B};
-  if (fork) cudaEventRecord(c->ev_f2, s);  // the weight-gradient branch forks here, but is enqueued after the
+  if (fork && !mid) cudaEventRecord(c->ev_f2, s);  // the weight-gradient branch forks here, but is enqueued after the
   // data-gradient kernel below so that the critical-path kernel is dispatched first
   Conv14Args d2{c->dy2, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
   tc = false;
   if constexpr (!std::is_same<T, float>::value) {
-    if (c->use_tc) {
+    if (mid) {
+      tc = true;
+      BwdMidArgs ma{r2, static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dp1, c->y1, st1, c->bpart1_ll};
+      launch_k(k_bwd_mid_tc<T>, dim3(B, 2), dim3(MID_THREADS), MID_SMEM_BYTES, s, ma, pdl);
+      if (fork) cudaEventRecord(c->ev_f2, s);  // the weight-gradient branch needs this kernel's d(conv2 out) planes
+    } else if (c->use_tc) {
       tc = true;
       Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
       launch_k(k_conv2_tc<T, 2>, dim3(std::min(B, 296), tsplit), dim3(TC_THREADS), tc_smem_bytes(4), s, t2, pdl);
@@ -538,12 +558,13 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   }
   if (!wtc) k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s2>>>(w2);
   mark();
-  k_reduce_rows<<<25, 128, 0, s2>>>(c->gpart, c->gred, gw_rows); mark();
+  k_reduce_rows<<<mid ? 26 : 25, 128, 0, s2>>>(c->gpart, c->gred, gw_rows, mid ? 2 * B : 0); mark();
   if (fork) cudaEventRecord(c->ev_j2, s2);
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
-  const int ns1 = clampi(B, 1, 32);  // one image per CTA at small batch: every thread has a single window, a single trip to L2
+  const int ns1 = mid ? 2 * B : clampi(B, 1, 32);  // one image per CTA at small batch: every thread has a single window, a single trip to L2
   BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->defer_stats == 2 ? c->bpart1_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, c->defer_stats, ns1, nullptr, nullptr, c->gpart};
-  launch_k(k_bn_bwd_reduce<T, 16, 28>, dim3(16, ns1), dim3(256), 0, s, r1, pdl); mark();
+  if (!mid) { launch_k(k_bn_bwd_reduce<T, 16, 28>, dim3(16, ns1), dim3(256), 0, s, r1, pdl); mark(); }
+  else skip_slot();
   const int gc1 = std::min(B, 296);
   Conv1WgradArgs cw{r1, x};
   if (rec) rec->a_c1w = cw;
@@ -562,7 +583,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   mark();
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->host_mail, c->bnbuf, c->nbt, c->ds, c->comm, B,
-              rows_c1, gw_rows, planes ? ns2p : ns2, nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval,
+              rows_c1, gw_rows, mid ? 0 : (planes ? ns2p : ns2), nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval,
               c->mom, cfg.momentum, cfg.weight_decay, cfg.dampening, cfg.nesterov};
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();

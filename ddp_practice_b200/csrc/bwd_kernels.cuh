@@ -530,6 +530,13 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
   // Phase A, part 1 for one image: the input tile into shared memory and this thread's five pooling windows
   // (conv1 output + incoming gradient) into registers -- all loads issued together
   float wv[5][4], wd[5];
+  auto fetch_grad = [&](int n) {  // d(pool1 out): may come from the direct predecessor, so only after the wait
+#pragma unroll
+    for (int it = 0; it < 5; ++it) {
+      const int e = min(tid + it * C1W_THREADS, 783);
+      wd[it] = ldf<T>(&dp1[((size_t)n * 16 + cg * 4 + e / 196) * 196 + e % 196]);
+    }
+  };
   auto fetch = [&](int n) {
     for (int i = tid; i < 196; i += C1W_THREADS) {
       const float4 v = load_pixels4(a.x, n, i);
@@ -543,20 +550,19 @@ __global__ void __launch_bounds__(C1W_THREADS) k_conv1_wgrad(Conv1WgradArgs a) {
       const size_t off = (((size_t)n * 16 + c) * 28 + 2 * ph) * 28 + 2 * pw;
       load2<T>(y1 + off, wv[it][0], wv[it][1]);
       load2<T>(y1 + off + 28, wv[it][2], wv[it][3]);
-      wd[it] = ldf<T>(&dp1[((size_t)n * 16 + c) * 196 + w]);
     }
   };
-  // None of this depends on the predecessor (BN1 backward pass 1), only on kernels before it, which are complete
-  // once this grid runs: the first image is fetched BEFORE waiting for the sums
+  // The input and conv1's output do not depend on the predecessor, only on kernels before it, which are complete
+  // once this grid runs: the first image is fetched BEFORE waiting for the sums, its incoming gradient right after
   __syncthreads();
   if ((int)blockIdx.x < a.bn.B) fetch(blockIdx.x);
-  bn_backward_sums<16>(a.bn, s_k1, s_k2);
+  bn_backward_sums<16>(a.bn, s_k1, s_k2, [&] { if ((int)blockIdx.x < a.bn.B) fetch_grad(blockIdx.x); });
   if (threadIdx.x == 0) TRACE(12 * 16 + 1);
   if (tid < 4) { s_cst[tid][4] = s_k1[cg * 4 + tid]; s_cst[tid][5] = s_k2[cg * 4 + tid]; }
 
   for (int n = blockIdx.x; n < a.bn.B; n += gridDim.x) {
     __syncthreads();
-    if (n != (int)blockIdx.x) fetch(n);
+    if (n != (int)blockIdx.x) { fetch(n); fetch_grad(n); }
 #pragma unroll
     for (int it = 0; it < 5; ++it) {
       const int e = tid + it * C1W_THREADS;

@@ -26,7 +26,8 @@ struct StepArgs {
   float* grads;         // tap T-c
   float* grads_scaled;  // tap T-b
   const float* gpart;   // [rows][N_PAD]
-  const float* gred;    // [N_PAD] conv2-weight partial rows already summed (k_reduce_rows), or null
+  const float* gred;    // [N_PAD] conv2-weight partial rows already summed (k_reduce_rows), or null; rows_conv2b == 0:
+                        // the conv2 bias gradient as well
   const float* gdirect; // [N_PAD]
   const float* nll;     // [B]
   volatile float* host_mail;  // pinned host memory {loss, step counter as float bits}: lets the host API return the
@@ -57,9 +58,10 @@ struct StepArgs {
 // Sum the conv2 weight-gradient partial rows (one per wgrad CTA) in fixed row order, spread
 // over many SMs; runs on a side branch of the step graph, off the critical path, so that the
 // 8-CTA tail kernel reads one row instead of pulling rows x 51 KB through 8 SMs' L2 ports.
-__global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ gpart, float* __restrict__ gred, int rows) {
+__global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ gpart, float* __restrict__ gred, int rows, int rows_bias) {
   const int i = (blockIdx.x * 128 + threadIdx.x) * 4;
-  if (i >= 12800) return;
+  if (i >= 12800 + (rows_bias > 0 ? 32 : 0)) return;
+  if (i >= 12800) rows = rows_bias;  // the conv2 bias gradient right behind the filter (bwd_mid_tc.cuh writes 2B rows)
   const float* p = gpart + OFF_W2 + i;
   float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 8
@@ -148,7 +150,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
       g = make_float4(rnd<T>(pre.x), rnd<T>(pre.y), rnd<T>(pre.z), rnd<T>(pre.w));
     } else if (round_t) {
       const float* p = a.gpart + e;
-      if (a.gred != nullptr && e >= OFF_W2 && e < OFF_B2) { p = a.gred + e; rows = 1; }
+      if (a.gred != nullptr && e >= OFF_W2 && e < (a.rows_conv2b == 0 ? OFF_G2 : OFF_B2)) { p = a.gred + e; rows = 1; }
       if (e < OFF_G1) {  // conv1 region: lanes summed above, combine in fixed order
         rows = 0;
 #pragma unroll

@@ -407,3 +407,11 @@ def test_eval_batch_size_boundaries_match_oracle(dtype, batch):
     c, s = e.read_counts()
     assert s == float(batch) and c == float((got.argmax(1) == y).sum())
     e.close()
+
+
+def test_fused_backward_middle_kernel_matches_oracle(monkeypatch):
+    """DDPSTEP_MID=1 (opt-in, bwd_mid_tc.cuh): BN2 backward apply + conv2 data gradient + BN1 backward pass 1 as one
+    tcgen05 kernel per (image, M-tile).  Same parity bar as the default path."""
+    monkeypatch.setenv("DDPSTEP_MID", "1")
+    _check_steps_against_oracle("fp16", 32, 3, 32)
+    _check_steps_against_oracle("bf16", 12, 3, 32)
