@@ -275,9 +275,17 @@ def main():
     # nodes, i.e. the instrumentation overhead every other interval contains; it is subtracted from the kernel times
     empty = [-v for v in prof.values() if v < 0]
     ev_overhead = sum(empty) / len(empty) if empty else 0.0
+    fused_away = [k for k, v in prof.items() if v < 0]
     prof = {k: max(v - ev_overhead, 0.0) for k, v in prof.items() if v >= 0}
+    # a kernel that hosts another stage at this batch size also moves that stage's bytes
+    hosts = {"w2_tiles_refresh": "conv1_fwd", "bn2_relu_pool": "fc_ce", "bn2_bwd_reduce": "fc_ce",
+             "bn2_bwd_apply": "conv2_dgrad", "bn1_bwd_reduce": "conv2_dgrad"}
+    work = dict(KERNEL_WORK)
+    for k in fused_away:
+        h = hosts[k]
+        work[h] = tuple(a + b for a, b in zip(work[h], KERNEL_WORK[k]))
     dom = max((k for k in prof if k not in ("step", "conv2_wgrad_reduce", "w2_tiles_refresh")), key=lambda k: prof[k])
-    fl, ab, xb = KERNEL_WORK[dom]
+    fl, ab, xb = work[dom]
     sec = prof[dom] * 1e-3
     if fl >= 627200 and dom.startswith("conv2"):
         ach = fl * B / sec / 1e12
@@ -292,7 +300,7 @@ def main():
     roof.update({"traffic": traffic, "peak_source": peak_src, "avg_kernel_us": prof[dom] * 1e3,
                  "how": f"CUDA events between the kernel nodes of the step graph, mean of {n_prof} steps, minus the "
                         f"measured interval of an empty slot ({ev_overhead * 1e3:.2f} us)",
-                 "event_overhead_us": round(ev_overhead * 1e3, 2),
+                 "event_overhead_us": round(ev_overhead * 1e3, 2), "stages_fused_into_other_kernels": fused_away,
                  "kernel_us": {k: round(v * 1e3, 2) for k, v in prof.items()},
                  "step_hbm_frac": (STEP_BYTES_PER_IMG_AMP * (es / 2) * B + STEP_PARAM_BYTES) / (ms_total / K * 1e-3) / 1e9 / hbm_peak,
                  "note": "batch 32 is latency-bound (SURVEY.md 8d): 7.9 MB and 0.52 GFLOP per step"})
