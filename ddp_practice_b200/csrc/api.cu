@@ -551,6 +551,10 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
     if (c->use_tc && c->use_wgrad_tc) {
       wtc = true;
       gw_rows = std::min(B, 148);
+      // small batches: several images per CTA (the accumulators stay in TMEM) keep the 5-way kh split within one
+      // wave of SMs and shorten the row reduction behind it; DDPSTEP_WG_DIV overrides the images-per-CTA choice
+      static const int wg_div = [] { const char* e = getenv("DDPSTEP_WG_DIV"); return e ? std::max(1, atoi(e)) : 2; }();  // measured at batch 32: 1 -> 45.1, 2 -> 43.0, 4 -> 44.7 us per step
+      if (B <= 64) gw_rows = cdiv(B, wg_div);
       Conv2WgradTcArgs wa{c->dy2h, c->p1h, c->gpart, B};
       // small batches: split the 5 kh taps over 5 CTAs per image so more SMs take part
       k_conv2_wgrad_tc<T><<<dim3(gw_rows, B <= 64 ? 5 : 1), TC_THREADS, WG_SMEM_BYTES, s2>>>(wa);

@@ -64,10 +64,13 @@ __global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ g
   if (i >= 12800) rows = rows_bias;  // the conv2 bias gradient right behind the filter (bwd_mid_tc.cuh writes 2B rows)
   const float* p = gpart + OFF_W2 + i;
   float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-  for (int r = 0; r < rows; ++r) {
-    const float4 v = __ldcg(reinterpret_cast<const float4*>(p + (size_t)r * N_PAD));
-    g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+  for (int r0 = 0; r0 < rows; r0 += 16) {  // sixteen predicated loads per trip to L2, row order kept
+    float4 v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      v[i] = r0 + i < rows ? __ldcg(reinterpret_cast<const float4*>(p + (size_t)(r0 + i) * N_PAD)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) { g.x += v[i].x; g.y += v[i].y; g.z += v[i].z; g.w += v[i].w; }
   }
   *reinterpret_cast<float4*>(gred + OFF_W2 + i) = g;
 }
