@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(224) k_fc_wgrad(FcWgradArgs a) {
 #pragma unroll
   for (int j = 0; j < 10; ++j) row[OFF_WFC + j * 1568 + k] = acc[j];
   if (blockIdx.x == 0 && tid < 10) row[OFF_BFC + tid] = bsum;
+  if (threadIdx.x == 0) TRACE(6 * 16 + 15);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -440,6 +440,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
   if (warp == 0) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+    if (threadIdx.x == 0) TRACE(8 * 16 + 15);
   }
 }
 

@@ -59,6 +59,7 @@ struct StepArgs {
 // over many SMs; runs on a side branch of the step graph, off the critical path, so that the
 // 8-CTA tail kernel reads one row instead of pulling rows x 51 KB through 8 SMs' L2 ports.
 __global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ gpart, float* __restrict__ gred, int rows, int rows_bias) {
+  if (threadIdx.x == 0) TRACE(14 * 16 + 0);
   const int i = (blockIdx.x * 128 + threadIdx.x) * 4;
   if (i >= 12800 + (rows_bias > 0 ? 32 : 0)) return;
   if (i >= 12800) rows = rows_bias;  // the conv2 bias gradient right behind the filter (bwd_mid_tc.cuh writes 2B rows)
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ g
     for (int i = 0; i < 16; ++i) { g.x += v[i].x; g.y += v[i].y; g.z += v[i].z; g.w += v[i].w; }
   }
   *reinterpret_cast<float4*>(gred + OFF_W2 + i) = g;
+  if (threadIdx.x == 0) TRACE(14 * 16 + 15);
 }
 
 template <typename T>

@@ -21,7 +21,7 @@ for i in range(50): e.train_step(x, y)
 torch.cuda.synchronize()
 buf = (C.c_ulonglong * 256)(); lib.ddpstep_read_trace(buf); t = list(buf)
 names = ["w2_tiles_refresh", "conv1_fwd", "bn1_relu_pool", "conv2_fwd", "bn2_relu_pool", "fc_ce", "fc_wgrad", "bn2_bwd_reduce",
-         "conv2_wgrad", "bn2_bwd_apply", "conv2_dgrad", "bn1_bwd_reduce", "conv1_wgrad", "step"]
+         "conv2_wgrad", "bn2_bwd_apply", "conv2_dgrad", "bn1_bwd_reduce", "conv1_wgrad", "step", "conv2_wgrad_reduce"]
 ev = [(t[16 * k], names[k], k) for k in range(len(names)) if t[16 * k]]
 ev.sort(); base = ev[0][0]
 for ts, n, k in ev:
