@@ -121,8 +121,13 @@ int ddpstep_state_ptrs(ddpstep_ctx* ctx, ddpstep_ptrs* out);
  * graph replay.  x: [batch,1,28,28] fp32, y: [batch] int64, both DEVICE pointers.          */
 int ddpstep_train_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
                        void* stream);
-/* Same, from HOST buffers (the `.cuda()` copies of ddp_main.py:86-87 included); if loss_out
- * is not NULL the loss is copied back and the call synchronises the stream.                 */
+/* Same, from HOST buffers (the `.cuda()` copies of ddp_main.py:86-87 included).  Pinned
+ * buffers (cudaHostAlloc / pin_memory()) are copied by two nodes of the step graph itself,
+ * pageable ones by ordinary stream-ordered copies.  If loss_out is not NULL the call returns
+ * once the step has posted its loss (the tail kernel writes it into a pinned mailbox the call
+ * polls: no device-to-host copy, no stream synchronisation); with loss_out == NULL the call
+ * is asynchronous and, as with cudaMemcpyAsync, the host buffers must stay untouched until
+ * the stream has passed the step.                                                           */
 int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* x_host, const int64_t* y_host,
                             int32_t batch, float* loss_out, void* stream);
 
