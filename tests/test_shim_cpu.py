@@ -73,3 +73,43 @@ def test_reference_scripts_need_only_two_import_edits(script):
     assert methods == {"scale", "step", "update", "state_dict"}
     for m in methods:
         assert callable(getattr(shim.GradScaler, m))
+
+
+def test_sgd_hyper_parameters_are_read_from_the_param_group():
+    """the shim hands torch.optim.SGD's knobs to the fused tail kernel; unsupported ones fail loudly
+    before anything is launched."""
+    p = [tnn.Parameter(torch.zeros(3))]
+    g = torch.optim.SGD(p, 1e-2, momentum=0.9, weight_decay=5e-4, nesterov=True).param_groups[0]
+    assert shim._sgd_knobs(g) == dict(momentum=0.9, weight_decay=5e-4, dampening=0.0, nesterov=True)
+    assert shim._sgd_knobs(torch.optim.SGD(p, 1e-4).param_groups[0]) == dict(momentum=0.0, weight_decay=0.0,
+                                                                            dampening=0.0, nesterov=False)
+    with pytest.raises(NotImplementedError, match="maximize"):
+        shim.GradScaler().step(torch.optim.SGD(p, 1e-4, maximize=True))
+    two = torch.optim.SGD([{"params": p}, {"params": [tnn.Parameter(torch.zeros(2))]}], 1e-4)
+    with pytest.raises(NotImplementedError):
+        shim.GradScaler().step(two)
+
+
+def test_config_struct_mirrors_the_header():
+    """ctypes Config / Ptrs must list exactly the fields of ddpstep_config / ddpstep_ptrs in include/ddpstep.h, in order."""
+    import re
+    from ddp_practice_b200 import _lib
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "ddpstep.h")).read()
+
+    def fields(struct):
+        body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (struct, struct), src, re.S).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        names = []
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            rest = decl.split(None, 1)[1]  # drop the type
+            names += [n.strip().lstrip("*") for n in rest.split(",")]
+        return names
+
+    assert fields("ddpstep_config") == [n for n, _ in _lib.Config._fields_]
+    assert fields("ddpstep_ptrs") == [n for n, _ in _lib.Ptrs._fields_]
+    cfg = _lib.Config()
+    _lib.load().ddpstep_default_config(cfg)
+    assert cfg.abi_version == 2 and cfg.momentum == 0.0 and cfg.nesterov == 0 and abs(cfg.lr - 1e-4) < 1e-10
