@@ -201,3 +201,16 @@ def test_amp_fp16_momentum_dampening_matches_reference():
             assert_grads_close(r.grads, g["grads"][s], AMP_TOL, f"step {s}")
     fin = state_from_golden(g, "final_")
     assert_grads_close(st.flat_params() - ini.flat_params(), fin.flat_params() - ini.flat_params(), AMP_TOL, "update")
+
+
+def test_momentum_update_is_world_size_invariant_under_syncbn():
+    """Property: with SyncBN, W shards of the global batch give the global-batch gradient (finding 6), so the whole
+    optimizer tail -- weight decay, momentum buffer, nesterov -- must not depend on W either."""
+    g = load_golden("global_w4.npz")
+    kw = dict(lr=1e-2, momentum=0.9, weight_decay=5e-4, nesterov=True)
+    a, b = state_from_golden(g), state_from_golden(g)
+    for s, x, y in _steps(g):
+        O.train_step(a, [x], [y], dtype="fp32", use_scaler=False, **kw)
+        O.train_step(b, list(x.chunk(4)), list(y.chunk(4)), dtype="fp32", use_scaler=False, sync_bn=True, **kw)
+    assert_grads_close(a.momentum_buffer, b.momentum_buffer, 2e-5, "momentum buffer W=1 vs W=4")
+    assert torch.allclose(a.flat_params(), b.flat_params(), rtol=1e-5, atol=1e-6)
