@@ -22,9 +22,14 @@ def _newest_source_mtime():
     return m
 
 
+LAST_ACTION = "not built in this process"
+
+
 def build_library(force: bool = False, verbose: bool = False) -> str:
-    """Compile the CUDA library if it is missing or older than its sources."""
+    """Compile the CUDA library if it is missing or older than its sources; LAST_ACTION says which happened."""
+    global LAST_ACTION
     if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= _newest_source_mtime():
+        LAST_ACTION = "reused (library newer than every source by mtime)"
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -36,6 +41,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError(f"nvcc failed ({' '.join(cmd)}):\n{res.stdout}\n{res.stderr}")
     if verbose:
         print(res.stderr)
+    LAST_ACTION = "compiled with nvcc for sm_100a"
     return LIB_PATH
 
 

@@ -3,6 +3,7 @@
 #include "../../include/ddpstep.h"
 
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -10,6 +11,7 @@
 #include <type_traits>
 #include <mutex>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "bwd_kernels.cuh"
@@ -22,6 +24,9 @@
 using namespace dstep;
 
 static thread_local std::string g_create_error;
+
+// mode: 0 train, 1 eval; source: 0 float batch on the device, 1 uint8 dataset + indices, 2 pinned host batch
+typedef std::tuple<int, int, int, int> GraphKey;  // (mode, source, has_labels, batch)
 
 struct GraphEntry {
   cudaGraphExec_t exec = nullptr;
@@ -40,6 +45,7 @@ struct GraphEntry {
   BatchSrc x = {nullptr, nullptr, nullptr};
   const int64_t* y = nullptr;
   int n_kernels = 0;
+  bool planes = false;  // p1 / d(conv2 out) exist only as padded planes after this graph ran (ddpstep_read_activation)
   // host-fed variant (ddpstep_train_step_host): the two H2D copies are nodes of the graph
   cudaGraphNode_t node_hx = nullptr, node_hy = nullptr;
   const void *hx = nullptr, *hy = nullptr;
@@ -78,8 +84,8 @@ struct ddpstep_ctx {
   CommDev comm;
   bool peers_ready = false;
   std::vector<void*> opened;
-  // graphs, keyed by batch (train) / -batch (eval with labels) / -batch-100000 (eval, no labels)
-  std::map<long, GraphEntry> graphs;
+  // one captured graph per (mode, where the batch comes from, labels present, batch size)
+  std::map<GraphKey, GraphEntry> graphs;
   cudaStream_t cap_stream = nullptr, side1 = nullptr, side2 = nullptr;
   cudaEvent_t ev_f0 = nullptr, ev_j0 = nullptr, ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
   cudaEvent_t ev_h0 = nullptr, ev_h1 = nullptr;
@@ -87,6 +93,10 @@ struct ddpstep_ctx {
   float* mom = nullptr;   // SGD momentum buffers, same flat layout as the parameters
   volatile float* host_mail = nullptr;  // pinned, mapped: {loss, completed-step counter}
   unsigned int steps_enqueued = 0;     // training steps launched so far (matches DevState.epoch once they finish)
+  int sm_khz = 1965000;                // SM clock used to turn the peer timeout into clock64() cycles
+  StepArgs last_step;                  // arguments of the most recently enqueued tail kernel (ddpstep_allreduce_only)
+  int last_step_dtype_ok = 0;
+  int cap_bn1 = 0, cap_bn2 = 0, cap_bwd2 = 0, cap_c1w = 0;  // CTAs of the BN consumer kernels the device holds at once (occupancy API)
   int64_t launches = 0;
   int esize = 2;
 };
@@ -192,6 +202,16 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   DevState h;
   memset(&h, 0, sizeof h);
   h.scale = cfg->use_scaler ? cfg->init_scale : 1.0f;
+  h.lr = cfg->lr; h.momentum = cfg->momentum; h.weight_decay = cfg->weight_decay; h.dampening = cfg->dampening;
+  h.nesterov = cfg->nesterov;
+  ctx->sm_khz = prop.clockRate > 0 ? prop.clockRate : 1965000;
+  {
+    // default peer timeout: 20 s (a rank may legitimately be seconds late: first-batch DataLoader start, a rank-0
+    // checkpoint, a graph capture); DDPSTEP_PEER_TIMEOUT_MS or ddpstep_set_peer_timeout_ms change it
+    const char* et = getenv("DDPSTEP_PEER_TIMEOUT_MS");
+    const double ms = et ? atof(et) : 20000.0;
+    h.timeout_cycles = (long long)(ms * (double)ctx->sm_khz);
+  }
   cudaError_t e = cudaMemcpy(ctx->bnbuf, bn.data(), N_BNBUF * 4, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(ctx->ds, &h, sizeof h, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->cap_stream, cudaStreamNonBlocking);
@@ -217,6 +237,28 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(2));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__half, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_tc<__nv_bfloat16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc_smem_bytes(4));
+  if (e == cudaSuccess) {
+    // Early publication (DDPSTEP_DEFER=2): the CTAs of a BN consumer grid spin on words that CTA 0 of the
+    // SAME grid publishes.  CUDA promises no dispatch order, so the scheme is only used for grids that are resident
+    // all at once according to the occupancy API (checked per launch in enqueue_train); larger grids let every
+    // consumer CTA reduce the rows itself (the DEFER=1 scheme).
+    int occ[3] = {0, 0, 0}, occ_c1w = 0;
+    const void* f[3];
+    switch (cfg->dtype) {
+      case DDPSTEP_FP32: f[0] = (const void*)k_bn_relu_pool<float, 16, 28>; f[1] = (const void*)k_bn_relu_pool<float, 32, 14>; f[2] = (const void*)k_bn2_bwd_apply<float>; break;
+      case DDPSTEP_FP16: f[0] = (const void*)k_bn_relu_pool<__half, 16, 28>; f[1] = (const void*)k_bn_relu_pool<__half, 32, 14>; f[2] = (const void*)k_bn2_bwd_apply<__half>; break;
+      default: f[0] = (const void*)k_bn_relu_pool<__nv_bfloat16, 16, 28>; f[1] = (const void*)k_bn_relu_pool<__nv_bfloat16, 32, 14>; f[2] = (const void*)k_bn2_bwd_apply<__nv_bfloat16>; break;
+    }
+    for (int i = 0; i < 3; ++i)
+      if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[i], f[i], 256, 0);
+    ctx->cap_bn1 = occ[0] * prop.multiProcessorCount;
+    ctx->cap_bn2 = occ[1] * prop.multiProcessorCount;
+    ctx->cap_bwd2 = occ[2] * prop.multiProcessorCount;
+    const void* fw = cfg->dtype == DDPSTEP_FP32 ? (const void*)k_conv1_wgrad<float>
+                   : cfg->dtype == DDPSTEP_FP16 ? (const void*)k_conv1_wgrad<__half> : (const void*)k_conv1_wgrad<__nv_bfloat16>;
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c1w, fw, C1W_THREADS, 0);
+    ctx->cap_c1w = occ_c1w * prop.multiProcessorCount;
+  }
   if (e != cudaSuccess) {
     fail(nullptr, DDPSTEP_E_CUDA, "context setup failed: %s", cudaGetErrorString(e));
     ddpstep_destroy(ctx);
@@ -431,8 +473,17 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   // conv2 on the tensor cores writes one partial row per (image CTA, M-tile): 2B rows at small batch.  The tagged-row
   // scheme reads at most 64 rows; between 33 and 64 images the plain deferred scheme (any row count) takes over.
   const int rows2 = std::min(B, 296) * ((!std::is_same<T, float>::value && c->use_tc) ? tsplit : 1);
-  const int defer1 = g1 <= 64 ? c->defer_stats : 0;
-  const int defer2 = std::min(B, 296) > 64 ? 0 : (rows2 <= 64 ? c->defer_stats : std::min(c->defer_stats, 1));
+  // tagged rows + early publication only for consumer grids that are fully co-resident (see ddpstep_create)
+  const int grid_bn1 = clampi(cdiv(B * 16 * 196, 256), 1, 1184), grid_bn2 = clampi(cdiv(B * 32 * 49, 256), 1, 1184);
+  int defer1 = g1 <= 64 ? c->defer_stats : 0;
+  if (defer1 == 2 && grid_bn1 > c->cap_bn1) defer1 = 1;
+  int defer2 = std::min(B, 296) > 64 ? 0 : (rows2 <= 64 ? c->defer_stats : std::min(c->defer_stats, 1));
+  if (defer2 == 2 && grid_bn2 > c->cap_bn2) defer2 = 1;
+  // the same rule for the two backward reductions: their consumers are k_bn2_bwd_apply(_planes) (<= 512 CTAs) and the
+  // conv1 weight-gradient kernel (<= 1184 CTAs of 160 threads on the CUDA-core path, <= 296 on the tensor-core one)
+  const int dstat2 = (c->defer_stats == 2 && 32 * 16 > c->cap_bwd2) ? 1 : c->defer_stats;
+  const bool cuda_core_c1w = std::is_same<T, float>::value || !(c->use_tc && c->use_conv1_tc && c->use_conv1_wgrad_tc && B > 64);
+  const int dstat1 = (c->defer_stats == 2 && cuda_core_c1w && std::min(B, 296) * 4 > c->cap_c1w) ? 1 : c->defer_stats;
   Conv1Args a1{x, c->params, c->y1, defer1 == 2 ? c->part1_ll : c->part1, defer1, st1, c->ds, c->comm, B, dbl, sync, cfg.bn_eps,
                tiles_in_conv1 ? c->w2_tiles : nullptr, g1};
   constexpr int kTileCtas = 25600 / (C1_GROUPS * C1_THREADS);  // 50 extra blockIdx.x values x 4 groups x 128 threads
@@ -484,7 +535,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
                 defer2 == 2 ? c->part2_ll : defer2 ? c->part2 : nullptr, tc ? g2 * tsplit : g2, defer2 == 2};
   // small batch: BN2's backward pass 1 rides in the Linear+CE kernel (one image per CTA, one tagged partial row per
   // image), and so does BN2 + ReLU + pool itself when conv2 left tagged rows (`head`: slot 4 stays empty)
-  const bool fuse_bn2r = c->defer_stats == 2 && B <= 64;
+  const bool fuse_bn2r = dstat2 == 2 && B <= 64;
   const bool head = fuse_bn2r && defer2 == 2 && c->fuse_head;
   if (!head) { launch_k(k_bn_relu_pool<T, 32, 14>, dim3(clampi(cdiv(B * 32 * 49, 256), 1, 1184)), dim3(256), 0, s, b2, pdl); mark(); }
   else skip_slot();
@@ -503,7 +554,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   if (fork) cudaEventRecord(c->ev_j1, s1);
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);  // batch splits of the two BN2 backward kernels
-  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, c->defer_stats == 2 ? c->bpart2_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, c->defer_stats,
+  BnBwdArgs r2{c->y2, c->dflat, c->params, st2, dstat2 == 2 ? c->bpart2_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns2), 1, sync, dstat2,
                fuse_bn2r ? B : ns2 /* partial rows per channel */, c->dy2, c->use_tc ? c->dy2h : nullptr, c->gpart};
   // the plane-writing apply kernel has 4 channel groups per batch split: use more splits to fill the GPU
   const int ns2p = clampi(cdiv(B, 2), 1, 64);
@@ -566,7 +617,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   if (fork) cudaEventRecord(c->ev_j2, s2);
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
   const int ns1 = mid ? 2 * B : clampi(B, 1, 32);  // one image per CTA at small batch: every thread has a single window, a single trip to L2
-  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, c->defer_stats == 2 ? c->bpart1_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, c->defer_stats, ns1, nullptr, nullptr, c->gpart};
+  BnBwdArgs r1{c->y1, c->dp1, c->params, st1, dstat1 == 2 ? c->bpart1_ll : c->bpart, c->gdirect, c->ds, c->comm, B, cdiv(B, ns1), 0, sync, dstat1, ns1, nullptr, nullptr, c->gpart};
   if (!mid) { launch_k(k_bn_bwd_reduce<T, 16, 28>, dim3(16, ns1), dim3(256), 0, s, r1, pdl); mark(); }
   else skip_slot();
   const int gc1 = std::min(B, 296);
@@ -587,8 +638,10 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   mark();
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->host_mail, c->bnbuf, c->nbt, c->ds, c->comm, B,
-              rows_c1, gw_rows, mid ? 0 : (planes ? ns2p : ns2), nsf, cfg.use_scaler, sync, cfg.lr, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval,
-              c->mom, cfg.momentum, cfg.weight_decay, cfg.dampening, cfg.nesterov};
+              rows_c1, gw_rows, mid ? 0 : (planes ? ns2p : ns2), nsf, cfg.use_scaler, sync, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval,
+              c->mom};
+  c->last_step = sa;
+  c->last_step_dtype_ok = 1;
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();
   return cudaGetLastError();
@@ -681,7 +734,7 @@ static int repoint(ddpstep_ctx* ctx, GraphEntry& ge, cudaGraphNode_t node, void*
 // so the 13 kernels are replayed with a single cudaGraphLaunch.
 template <bool TRAIN>
 static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int B, cudaStream_t s) {
-  const long key = (TRAIN ? (long)B : (y ? -(long)B : -(long)B - 100000)) + (x.x == nullptr ? 10000000L : 0L);
+  const GraphKey key(TRAIN ? 0 : 1, x.x == nullptr ? 1 : 0, y != nullptr ? 1 : 0, B);
   auto it = ctx->graphs.find(key);
   if (it == ctx->graphs.end()) {
     GraphEntry ge;
@@ -691,9 +744,14 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
     cudaError_t e = enqueue<TRAIN>(ctx, x, y, B, ctx->cap_stream, &rec);
     cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &ge.graph);
     ctx->launches = before;
-    if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "launch during capture failed: %s", cudaGetErrorString(e));
-    if (e2 != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "graph capture failed: %s", cudaGetErrorString(e2));
-    CK(cudaGraphInstantiate(&ge.exec, ge.graph, 0));
+    if (e != cudaSuccess || e2 != cudaSuccess) {
+      if (ge.graph) cudaGraphDestroy(ge.graph);
+      return fail(ctx, DDPSTEP_E_CUDA, "graph capture failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+    }
+    if (cudaError_t e3 = cudaGraphInstantiate(&ge.exec, ge.graph, 0); e3 != cudaSuccess) {
+      cudaGraphDestroy(ge.graph);
+      return fail(ctx, DDPSTEP_E_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e3));
+    }
     size_t n = 0;
     CK(cudaGraphGetNodes(ge.graph, nullptr, &n));
     std::vector<cudaGraphNode_t> nodes(n);
@@ -711,10 +769,13 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
       else if (p.func == kp.c1w) ge.node_c1w = nd;
       else if (kp.c1wtc && p.func == kp.c1wtc) { ge.node_c1w = nd; ge.c1wtc = true; }
     }
-    if (!ge.node_c1 || !ge.node_fc || (TRAIN && !ge.node_c1w))
+    if (!ge.node_c1 || !ge.node_fc || (TRAIN && !ge.node_c1w)) {
+      cudaGraphExecDestroy(ge.exec); cudaGraphDestroy(ge.graph);
       return fail(ctx, DDPSTEP_E_STATE, "could not locate the input-consuming kernel nodes in the captured graph");
+    }
     ge.a_c1 = rec.a_c1; ge.a_fc = rec.a_fc; ge.a_c1w = rec.a_c1w; ge.a_c1tc = rec.a_c1tc; ge.a_c1wtc = rec.a_c1wtc;
     ge.x = x; ge.y = y; ge.n_kernels = rec.n;
+    ge.planes = ctx->last_planes;  // set by enqueue_* during the capture
     it = ctx->graphs.emplace(key, ge).first;
   }
   GraphEntry& ge = it->second;
@@ -740,6 +801,7 @@ static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int 
   }
   CK(cudaGraphLaunch(ge.exec, s));
   ctx->launches += ge.n_kernels;
+  ctx->last_planes = ge.planes;
   return 0;
 }
 
@@ -754,7 +816,7 @@ static bool is_pinned_host(const void* p) {
 // graph launch this saves two driver calls on the host and the stream-order gaps between three separately
 // submitted pieces of work.  A new pair of host pointers re-points the two copy nodes of the instantiated graph.
 static int run_graph_host(ddpstep_ctx* ctx, const float* xh, const int64_t* yh, int B, cudaStream_t s) {
-  const long key = 20000000L + B;
+  const GraphKey key(0, 2, 1, B);
   const size_t xb = (size_t)B * 784 * 4, yb = (size_t)B * 8;
   auto it = ctx->graphs.find(key);
   if (it == ctx->graphs.end()) {
@@ -771,9 +833,14 @@ static int run_graph_host(ddpstep_ctx* ctx, const float* xh, const int64_t* yh, 
     cudaError_t e = enqueue<true>(ctx, BatchSrc{ctx->x_stage, nullptr, nullptr}, ctx->y_stage, B, ctx->cap_stream, &rec);
     cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &ge.graph);
     ctx->launches = before;
-    if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "launch during capture failed: %s", cudaGetErrorString(e));
-    if (e2 != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "graph capture failed: %s", cudaGetErrorString(e2));
-    CK(cudaGraphInstantiate(&ge.exec, ge.graph, 0));
+    if (e != cudaSuccess || e2 != cudaSuccess) {
+      if (ge.graph) cudaGraphDestroy(ge.graph);
+      return fail(ctx, DDPSTEP_E_CUDA, "graph capture failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+    }
+    if (cudaError_t e3 = cudaGraphInstantiate(&ge.exec, ge.graph, 0); e3 != cudaSuccess) {
+      cudaGraphDestroy(ge.graph);
+      return fail(ctx, DDPSTEP_E_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e3));
+    }
     size_t n = 0;
     CK(cudaGraphGetNodes(ge.graph, nullptr, &n));
     std::vector<cudaGraphNode_t> nodes(n);
@@ -787,8 +854,12 @@ static int run_graph_host(ddpstep_ctx* ctx, const float* xh, const int64_t* yh, 
       if (mp.dstPtr.ptr == ctx->x_stage) ge.node_hx = nd;
       else if (mp.dstPtr.ptr == ctx->y_stage) ge.node_hy = nd;
     }
-    if (!ge.node_hx || !ge.node_hy) return fail(ctx, DDPSTEP_E_STATE, "could not locate the copy nodes in the captured graph");
+    if (!ge.node_hx || !ge.node_hy) {
+      cudaGraphExecDestroy(ge.exec); cudaGraphDestroy(ge.graph);
+      return fail(ctx, DDPSTEP_E_STATE, "could not locate the copy nodes in the captured graph");
+    }
     ge.hx = xh; ge.hy = yh; ge.n_kernels = rec.n;
+    ge.planes = ctx->last_planes;
     it = ctx->graphs.emplace(key, ge).first;
   }
   GraphEntry& ge = it->second;
@@ -802,6 +873,16 @@ static int run_graph_host(ddpstep_ctx* ctx, const float* xh, const int64_t* yh, 
   }
   CK(cudaGraphLaunch(ge.exec, s));
   ctx->launches += ge.n_kernels;
+  ctx->last_planes = ge.planes;
+  return 0;
+}
+
+// A cross-rank wait timed out in an earlier step: the tail kernel raised word 2 of the pinned mailbox.  From then on
+// every step entry point refuses to launch (the replicas can no longer be assumed identical).
+static int peer_failed(ddpstep_ctx* ctx) {
+  if (ctx->host_mail && reinterpret_cast<const volatile int*>(ctx->host_mail)[2] != 0)
+    return fail(ctx, DDPSTEP_E_PEER, "a peer did not answer within the timeout in an earlier step; that step and all later "
+                                     "ones applied no update -- this context is dead (restart the job from a checkpoint)");
   return 0;
 }
 
@@ -812,7 +893,7 @@ static int check_step_args(ddpstep_ctx* ctx, const void* x, int32_t batch) {
   if (batch < 1 || batch > ctx->cfg.batch_cap)
     return fail(ctx, DDPSTEP_E_ARG, "batch %d outside [1, batch_cap=%d]", batch, ctx->cfg.batch_cap);
   if (!ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "world > 1: call ddpstep_import_peers first");
-  return 0;
+  return peer_failed(ctx);
 }
 
 extern "C" int ddpstep_train_step(ddpstep_ctx* ctx, const float* x, const int64_t* y, int32_t batch, void* stream) {
@@ -821,12 +902,15 @@ extern "C" int ddpstep_train_step(ddpstep_ctx* ctx, const float* x, const int64_
   if (!y) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  ctx->steps_enqueued++;
   const BatchSrc src{x, nullptr, nullptr};
-  if (ctx->cfg.use_graph) return run_graph<true>(ctx, src, y, batch, s);
-  cudaError_t e = enqueue<true>(ctx, src, y, batch, s, nullptr);
-  if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
-  return 0;
+  if (ctx->cfg.use_graph) {
+    rc = run_graph<true>(ctx, src, y, batch, s);
+  } else {
+    cudaError_t e = enqueue<true>(ctx, src, y, batch, s, nullptr);
+    if (e != cudaSuccess) rc = fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
+  }
+  if (rc == 0) ctx->steps_enqueued++;  // only a step that was really launched will post its sequence number
+  return rc;
 }
 
 // SURVEY 8(f) N1, the step immediately before the hot path: torchvision MNIST -> ToTensor -> DataLoader -> .cuda()
@@ -840,7 +924,7 @@ static int check_indexed(ddpstep_ctx* ctx, const void* images, const void* label
     return fail(ctx, DDPSTEP_E_ARG, "batch %d outside [1, batch_cap=%d]", batch, ctx->cfg.batch_cap);
   if (!ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "world > 1: call ddpstep_import_peers first");
   (void)labels;
-  return 0;
+  return peer_failed(ctx);
 }
 
 extern "C" int ddpstep_train_step_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8, const int64_t* labels,
@@ -850,12 +934,15 @@ extern "C" int ddpstep_train_step_indexed(ddpstep_ctx* ctx, const uint8_t* image
   if (!labels) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  ctx->steps_enqueued++;
   const BatchSrc src{nullptr, images_u8, reinterpret_cast<const long long*>(idx)};
-  if (ctx->cfg.use_graph) return run_graph<true>(ctx, src, labels, batch, s);
-  cudaError_t e = enqueue<true>(ctx, src, labels, batch, s, nullptr);
-  if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
-  return 0;
+  if (ctx->cfg.use_graph) {
+    rc = run_graph<true>(ctx, src, labels, batch, s);
+  } else {
+    cudaError_t e = enqueue<true>(ctx, src, labels, batch, s, nullptr);
+    if (e != cudaSuccess) rc = fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
+  }
+  if (rc == 0) ctx->steps_enqueued++;
+  return rc;
 }
 
 extern "C" int ddpstep_eval_batch_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8, const int64_t* labels,
@@ -896,9 +983,9 @@ extern "C" int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* xh, const 
   // pinned batches: copies and step as one graph.  DDPSTEP_HOSTGRAPH=0 keeps the separate copies for comparison.
   static const bool host_graph = [] { const char* e = getenv("DDPSTEP_HOSTGRAPH"); return !(e && e[0] == '0'); }();
   if (!zero_copy && host_graph && ctx->cfg.use_graph && is_pinned_host(xh) && is_pinned_host(yh)) {
-    ctx->steps_enqueued++;
     rc = run_graph_host(ctx, xh, yh, batch, s);
     if (rc) return rc;
+    ctx->steps_enqueued++;
     xd = nullptr;
   } else if (xd == nullptr || yd == nullptr) {  // stage through the library's device buffers (fixed graph pointers)
     CK(cudaMemcpyAsync(ctx->x_stage, xh, (size_t)batch * 784 * 4, cudaMemcpyHostToDevice, s));
@@ -925,6 +1012,7 @@ extern "C" int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* xh, const 
       if (*seq != want) return fail(ctx, DDPSTEP_E_STATE, "the step finished without posting its loss");
     }
     *loss_out = ctx->host_mail[0];
+    return peer_failed(ctx);  // the step just awaited may be the one that timed out
   }
   return 0;
 }
@@ -1015,13 +1103,13 @@ extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int6
   if (!y || !ms_out || n_out < kTrainKernels) return fail(ctx, DDPSTEP_E_ARG, "need labels and room for 15 durations");
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  ctx->steps_enqueued++;
   std::vector<cudaEvent_t> evs;
   cudaEvent_t ev0;
   CK(cudaEventCreate(&ev0));
   Recorder rec;
   rec.events = &evs;
   cudaError_t e;
+  auto drop_events = [&] { cudaEventDestroy(ev0); for (cudaEvent_t ev : evs) cudaEventDestroy(ev); };
   if (in_graph) {
     cudaGraph_t graph;
     cudaGraphExec_t exec;
@@ -1033,29 +1121,33 @@ extern "C" int ddpstep_profile_step(ddpstep_ctx* ctx, const float* x, const int6
     e = enqueue<true>(ctx, BatchSrc{x, nullptr, nullptr}, y, batch, ctx->cap_stream, &rec);
     cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &graph);
     ctx->launches = before;
-    if (e != cudaSuccess || e2 != cudaSuccess)
+    if (e != cudaSuccess || e2 != cudaSuccess) {
+      if (e2 == cudaSuccess && graph) cudaGraphDestroy(graph);
+      drop_events();
       return fail(ctx, DDPSTEP_E_CUDA, "profile capture failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
-    CK(cudaGraphInstantiate(&exec, graph, 0));
-    CK(cudaGraphLaunch(exec, s));
-    ctx->launches += rec.n;
-    CK(cudaStreamSynchronize(s));
-    cudaGraphExecDestroy(exec);
+    }
+    e = cudaGraphInstantiate(&exec, graph, 0);
+    if (e == cudaSuccess) {
+      e = cudaGraphLaunch(exec, s);
+      if (e == cudaSuccess) { ctx->launches += rec.n; ctx->steps_enqueued++; e = cudaStreamSynchronize(s); }
+      cudaGraphExecDestroy(exec);
+    }
     cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { drop_events(); return fail(ctx, DDPSTEP_E_CUDA, "profile graph failed: %s", cudaGetErrorString(e)); }
   } else {
     rec.ev_stream = s;
-    CK(cudaEventRecord(ev0, s));
-    e = enqueue<true>(ctx, BatchSrc{x, nullptr, nullptr}, y, batch, s, &rec);
-    if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "profile launch failed: %s", cudaGetErrorString(e));
-    CK(cudaStreamSynchronize(s));
+    e = cudaEventRecord(ev0, s);
+    if (e == cudaSuccess) e = enqueue<true>(ctx, BatchSrc{x, nullptr, nullptr}, y, batch, s, &rec);
+    if (e == cudaSuccess) { ctx->steps_enqueued++; e = cudaStreamSynchronize(s); }
+    if (e != cudaSuccess) { drop_events(); return fail(ctx, DDPSTEP_E_CUDA, "profile launch failed: %s", cudaGetErrorString(e)); }
   }
   cudaEvent_t prev = ev0;
   for (size_t i = 0; i < evs.size() && i < (size_t)kTrainKernels; ++i) {
-    CK(cudaEventElapsedTime(&ms_out[i], prev, evs[i]));
+    if (cudaEventElapsedTime(&ms_out[i], prev, evs[i]) != cudaSuccess) { cudaGetLastError(); ms_out[i] = 0.f; }
     if (rec.skipped >> i & 1u) ms_out[i] = -ms_out[i];  // nothing ran in this slot: minus the bare event-to-event interval
     prev = evs[i];
   }
-  cudaEventDestroy(ev0);
-  for (cudaEvent_t ev : evs) cudaEventDestroy(ev);
+  drop_events();
   return 0;
 }
 
@@ -1067,7 +1159,62 @@ extern "C" int ddpstep_device_status(ddpstep_ctx* ctx) {
   CK(cudaDeviceSynchronize());
   DevState h;
   CK(cudaMemcpy(&h, ctx->ds, sizeof h, cudaMemcpyDeviceToHost));
-  if (h.error) return fail(ctx, DDPSTEP_E_PEER, "a peer did not raise its flag within the spin timeout");
+  if (h.error) return fail(ctx, DDPSTEP_E_PEER, "a peer did not answer within the spin timeout; steps since then applied no update");
+  return 0;
+}
+
+// torch.optim.SGD's param_groups[0] at run time (an LR scheduler, a hand-edited group): the values live in device
+// memory, so neither the context nor any captured graph has to be rebuilt.  Stream-ordered: steps enqueued after this
+// call on the same stream use the new values.  ddp_main.py:125 sets them once; torch/optim/sgd.py:425-465 reads them
+// every step.
+extern "C" int ddpstep_set_sgd(ddpstep_ctx* ctx, float lr, float momentum, float weight_decay, float dampening, int32_t nesterov,
+                               void* stream) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  if (momentum < 0.f || weight_decay < 0.f) return fail(ctx, DDPSTEP_E_ARG, "momentum and weight_decay must be >= 0");
+  if (nesterov && (momentum <= 0.f || dampening != 0.f))
+    return fail(ctx, DDPSTEP_E_ARG, "nesterov momentum requires a momentum and zero dampening");  // sgd.py:68
+  CK(cudaSetDevice(ctx->cfg.device));
+  struct { float lr, momentum, weight_decay, dampening; int nesterov; } h = {lr, momentum, weight_decay, dampening, nesterov ? 1 : 0};
+  static_assert(offsetof(DevState, nesterov) - offsetof(DevState, lr) == 16, "DevState hyper-parameter block");
+  // pageable source: the runtime stages it before returning, so `h` may go out of scope
+  CK(cudaMemcpyAsync(&ctx->ds->lr, &h, sizeof h, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  ctx->cfg.lr = lr; ctx->cfg.momentum = momentum; ctx->cfg.weight_decay = weight_decay; ctx->cfg.dampening = dampening;
+  ctx->cfg.nesterov = nesterov ? 1 : 0;
+  return 0;
+}
+
+// How long a kernel polls for a peer's words before it gives up (default 20 s, or DDPSTEP_PEER_TIMEOUT_MS).  NCCL in the
+// reference blocks until its watchdog fires; here a step whose wait expired applies no update and
+// every later call returns DDPSTEP_E_PEER.
+extern "C" int ddpstep_set_peer_timeout_ms(ddpstep_ctx* ctx, double ms) {
+  if (!ctx || !(ms > 0.0)) return fail(ctx, DDPSTEP_E_ARG, "timeout must be positive");
+  CK(cudaSetDevice(ctx->cfg.device));
+  const long long cycles = (long long)(ms * (double)ctx->sm_khz);
+  CK(cudaMemcpy(&ctx->ds->timeout_cycles, &cycles, sizeof cycles, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+// The tail kernel on its own: Reducer all-reduce of the 116,136-byte bucket fused with unscale / non-finite check /
+// SGD / scale update, re-run on the partial gradients the last training step left behind (state advances like a
+// step: the same gradient is applied again).  For measuring the exchange in isolation (tools/allreduce_bench.py,
+// bench.py `allreduce`); every rank must call it the same number of times.  Replaces the single ncclAllReduce behind
+// ddp_main.py:121-123 (reducer.hpp:524) + grad_scaler.py:294-298,371 + sgd.py:473.
+extern "C" int ddpstep_allreduce_only(ddpstep_ctx* ctx, void* stream) {
+  if (!ctx) return DDPSTEP_E_ARG;
+  if (!ctx->last_step_dtype_ok) return fail(ctx, DDPSTEP_E_STATE, "run a training step first: the tail kernel re-reduces its partial gradients");
+  int rc = peer_failed(ctx);
+  if (rc) return rc;
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  StepArgs sa = ctx->last_step;
+  switch (ctx->cfg.dtype) {
+    case DDPSTEP_FP32: launch_k(k_step<float>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+    case DDPSTEP_FP16: launch_k(k_step<__half>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+    default: launch_k(k_step<__nv_bfloat16>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+  }
+  CK(cudaGetLastError());
+  ctx->launches++;
+  ctx->steps_enqueued++;
   return 0;
 }
 
@@ -1108,6 +1255,12 @@ extern "C" int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const floa
   ddpstep_ctx* ctx = nullptr;  // errors are reported through ddpstep_last_error(NULL)
   if (!params_dev || !x_dev || !y1_dev || !stats_dev) return fail(nullptr, DDPSTEP_E_ARG, "null device pointer");
   if (dtype < 0 || dtype > 2) return fail(nullptr, DDPSTEP_E_ARG, "bad dtype %d", dtype);
+  // the kernel reads x with 16-byte loads and writes y1 with 8- / 16-byte stores: a misaligned sub-buffer of the
+  // caller's arena would raise a sticky misaligned-address fault in the caller's whole CUDA context
+  if ((reinterpret_cast<uintptr_t>(x_dev) & 15) || (reinterpret_cast<uintptr_t>(y1_dev) & 15))
+    return fail(nullptr, DDPSTEP_E_ARG, "x_dev and y1_dev must be 16-byte aligned");
+  if ((reinterpret_cast<uintptr_t>(params_dev) & 3) || (reinterpret_cast<uintptr_t>(stats_dev) & 3))
+    return fail(nullptr, DDPSTEP_E_ARG, "params_dev and stats_dev must be 4-byte aligned");
   if (batch < 1 || batch > NOALLOC_MAX_BATCH)
     return fail(nullptr, DDPSTEP_E_ARG,
                 "batch %d is outside [1, %d]: the allocation-free entry point keeps one row of partial sums per "

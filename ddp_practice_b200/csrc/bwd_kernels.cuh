@@ -209,7 +209,7 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, A
           for (int i = 0; i < 16; ++i) v[i] = __uint_as_float((unsigned int)w[i]);
           if (ok) break;
           if (spin == 64) t0 = clock64();
-          if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(&a.ds->error, 1); break; }
+          if (spin > 64 && spin_expired(t0, a.ds)) break;
         }
 #pragma unroll
         for (int i = 0; i < 16; ++i) acc += (double)v[i];  // rows past nsplit contribute +0.0
@@ -257,13 +257,13 @@ __device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, A
     } else if (polled && !xchg) {  // single rank: the words CTA (0,0) published
       float got[2];
       const int idx[2] = {c, C + c};
-      ll_gather<2, 1>(&a.comm.self->ll_bn_bwd[a.layer][a.comm.rank][0], 64, idx, 0, 1, tag, got, &a.ds->error);
+      ll_gather<2, 1>(&a.comm.self->ll_bn_bwd[a.layer][a.comm.rank][0], 64, idx, 0, 1, tag, got, a.ds);
       s0 = got[0]; s1 = got[1];
     } else if (xchg) {
       s0 = 0.f; s1 = 0.f;
       float got[MAX_WORLD * 2];
       const int idx[2] = {c, C + c};
-      ll_gather<2>(&a.comm.self->ll_bn_bwd[a.layer][0][0], 64, idx, 0, a.comm.world, tag, got, &a.ds->error);
+      ll_gather<2>(&a.comm.self->ll_bn_bwd[a.layer][0][0], 64, idx, 0, a.comm.world, tag, got, a.ds);
 #pragma unroll
       for (int r = 0; r < MAX_WORLD; ++r) {  // fixed rank order
         if (r < a.comm.world) { s0 += got[r * 2]; s1 += got[r * 2 + 1]; }

@@ -99,6 +99,14 @@ struct DevState {
   float found_inf;
   float loss;
   int mom_ready;                  // SGD momentum buffers hold values (set by the first executed step)
+  // Run-time hyper-parameters of torch.optim.SGD (param_groups[0]; sgd.py:425-465).  They live in device memory, not in
+  // kernel arguments, so an LR scheduler or a hand-edited param group changes them without a new context or graph
+  // (ddpstep_set_sgd).
+  float lr, momentum, weight_decay, dampening;
+  int nesterov;
+  // Cross-rank waits give up after this many SM clock cycles (ddpstep_set_peer_timeout_ms) and raise `error`; a step
+  // that saw the error applies no update (k_step) and the host API reports DDPSTEP_E_PEER.
+  long long timeout_cycles;
 };
 
 // global BN statistics of the current step, written by the bn_relu_pool kernel
@@ -136,15 +144,23 @@ __device__ __forceinline__ void store_partial(float* part, size_t i, float v, in
   if (ll) ll_store(reinterpret_cast<llword*>(part) + i, v, tag);
   else part[i] = v;
 }
-// Poll a word of this rank's own region until its tag matches; ~4 s timeout raises the error word.
-__device__ __forceinline__ float ll_wait(const llword* p, unsigned int tag, int* err) {
+// A cross-rank wait that has spun for longer than the configured timeout raises the sticky error word: the step
+// then applies no update (k_step) and the host API returns DDPSTEP_E_PEER -- a late or dead peer must never end in a
+// silently different replica.
+__device__ __forceinline__ bool spin_expired(long long t0, DevState* ds) {
+  if (*reinterpret_cast<volatile int*>(&ds->error) != 0) return true;  // the step is void already: do not wait again
+  if (clock64() - t0 > *reinterpret_cast<volatile long long*>(&ds->timeout_cycles)) { atomicExch(&ds->error, 1); return true; }
+  return false;
+}
+// Poll a word of this rank's own region until its tag matches (bounded by the peer timeout).
+__device__ __forceinline__ float ll_wait(const llword* p, unsigned int tag, DevState* ds) {
   llword w;
   long long t0 = 0;
   for (int spin = 0;; ++spin) {
     asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
     if ((unsigned int)(w >> 32) == tag) break;
     if (spin == 64) t0 = clock64();
-    if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(err, 1); break; }
+    if (spin > 64 && spin_expired(t0, ds)) break;
   }
   return __uint_as_float((unsigned int)w);
 }
@@ -158,8 +174,8 @@ __device__ __forceinline__ llword ll_ld(const llword* p) {
 // loads of one polling round are issued together, so a round costs ONE L2 round trip instead of
 // world x NW dependent ones; rounds repeat until every tag matches.  out[r*NW + j] = payload.
 template <int NW, int NR = MAX_WORLD>
-__device__ __forceinline__ void ll_gather(const llword* base, size_t stride, const int (&idx)[NW], int r0, int world,
-                                          unsigned int tag, float* out, int* err) {
+__device__ __forceinline__ bool ll_gather(const llword* base, size_t stride, const int (&idx)[NW], int r0, int world,
+                                          unsigned int tag, float* out, DevState* ds) {
   long long t0 = 0;
   for (int spin = 0;; ++spin) {
     llword w[NR * NW];
@@ -174,23 +190,23 @@ __device__ __forceinline__ void ll_gather(const llword* base, size_t stride, con
     if (ok) {
 #pragma unroll
       for (int i = 0; i < NR * NW; ++i) out[i] = __uint_as_float((unsigned int)w[i]);
-      return;
+      return true;
     }
     if (spin == 64) t0 = clock64();
-    if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(err, 1); return; }
+    if (spin > 64 && spin_expired(t0, ds)) {  // hand back what is there; the error word voids the step
+#pragma unroll
+      for (int i = 0; i < NR * NW; ++i) out[i] = __uint_as_float((unsigned int)w[i]);
+      return false;
+    }
   }
 }
 
-// Spin until *flag >= want; gives up after ~4 s and raises the error word so a dead peer
+// Spin until *flag >= want; gives up after the peer timeout and raises the error word so a dead peer
 // cannot hang the GPU forever.
-__device__ __forceinline__ void wait_flag(const unsigned long long* flag, unsigned long long want, int* err) {
+__device__ __forceinline__ void wait_flag(const unsigned long long* flag, unsigned long long want, DevState* ds) {
   long long t0 = clock64();
-  while (ld_acquire_sys(flag) < want) {
-    if (clock64() - t0 > 8000000000LL) {
-      atomicExch(err, 1);
-      break;
-    }
-  }
+  while (ld_acquire_sys(flag) < want)
+    if (spin_expired(t0, ds)) break;
 }
 
 // Programmatic dependent launch (PDL): inside the step graph a kernel may be launched while its
@@ -223,6 +239,17 @@ __device__ __forceinline__ bool last_cta_done(unsigned int* ticket, unsigned int
   __syncthreads();
   if (s_last) __threadfence();
   return s_last != 0;
+}
+
+// ReLU(max_pool 2x2) of four BN outputs as ATen computes it: a NaN in the window wins the pool
+// (`val > maxval || isnan(val)`) and passes the ReLU (`x <= 0 ? 0 : x`), so a poisoned forward reaches the loss and
+// GradScaler sees it.  fmaxf alone would drop the NaN.  The sum is NaN only for a NaN or inf - inf: one compare on
+// the hot path, the exact test only behind it.
+__device__ __forceinline__ float relu_max4(float v0, float v1, float v2, float v3) {
+  const float m = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
+  const float s = (v0 + v1) + (v2 + v3);
+  if (s != s && (v0 != v0 || v1 != v1 || v2 != v2 || v3 != v3)) return __int_as_float(0x7fc00000);
+  return m;
 }
 
 // The four BN outputs of one 2x2 pooling window and who wins the pool.

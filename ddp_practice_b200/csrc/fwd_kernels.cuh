@@ -314,7 +314,7 @@ __device__ void bn_local_stats(const BnPoolArgs& a, float local_count, unsigned 
         for (int i = 0; i < NV; ++i) v[i] = __uint_as_float((unsigned int)w[i]);
         if (ok) break;
         if (spin == 64) t0 = clock64();
-        if (spin > 64 && clock64() - t0 > 8000000000LL) { atomicExch(&a.ds->error, 1); break; }
+        if (spin > 64 && spin_expired(t0, a.ds)) break;
       }
     } else {
 #pragma unroll
@@ -411,7 +411,7 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
       float got[3];
       const int idx[3] = {c, C + c, 2 * C + c};
       ll_gather<3, 1>(&a.comm.self->ll_bn_fwd[a.layer][a.comm.rank][0], BN_FWD_SLOT, idx, 0, 1,
-                      (unsigned int)a.ds->epoch + 1u, got, &a.ds->error);
+                      (unsigned int)a.ds->epoch + 1u, got, a.ds);
       lmean = got[0]; linvstd = got[1]; lvar_unb = got[2];
     }
   } else if (!a.eval && c < C) {
@@ -430,7 +430,7 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
       const unsigned int tag = (unsigned int)a.ds->epoch + 1u;
       float got[MAX_WORLD * 3];
       const int idx[3] = {c, C + c, 3 * C};
-      ll_gather<3>(&a.comm.self->ll_bn_fwd[a.layer][0][0], BN_FWD_SLOT, idx, 0, a.comm.world, tag, got, &a.ds->error);
+      ll_gather<3>(&a.comm.self->ll_bn_fwd[a.layer][0][0], BN_FWD_SLOT, idx, 0, a.comm.world, tag, got, a.ds);
 #pragma unroll
       for (int r = 0; r < MAX_WORLD; ++r) {
         if (r >= a.comm.world) break;
@@ -456,12 +456,13 @@ __device__ void bn_forward_stats(const BnPoolArgs& a, float* s_mean, float* s_in
     if (blockIdx.x == 0 && !a.eval) {
       a.st->mean[c] = mean;
       a.st->invstd[c] = invstd;
-      if (c == 0) {
-        a.st->n_total = n_total;
-        a.nbt[a.layer] = own.nbt_old + 1;
+      if (c == 0) a.st->n_total = n_total;
+      // a timed-out statistics exchange must not leak into the running buffers (the step is void: k_step)
+      if (!xchg || *reinterpret_cast<volatile int*>(&a.ds->error) == 0) {
+        if (c == 0) a.nbt[a.layer] = own.nbt_old + 1;
+        a.bnbuf[rm_off + c] = (1.0f - a.momentum) * own.rm_old + a.momentum * mean;
+        a.bnbuf[rv_off + c] = (1.0f - a.momentum) * own.rv_old + a.momentum * var_unb;
       }
-      a.bnbuf[rm_off + c] = (1.0f - a.momentum) * own.rm_old + a.momentum * mean;
-      a.bnbuf[rv_off + c] = (1.0f - a.momentum) * own.rv_old + a.momentum * var_unb;
     }
   }
   __syncthreads();
@@ -507,7 +508,7 @@ __global__ void __launch_bounds__(256) k_bn_relu_pool(BnPoolArgs a) {
     v1 = rnd<T>((v1 - mu) * is * g + b);
     v2 = rnd<T>((v2 - mu) * is * g + b);
     v3 = rnd<T>((v3 - mu) * is * g + b);
-    const float m = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
+    const float m = relu_max4(v0, v1, v2, v3);
     stf<T>(&p[idx], m);
     if (C == 16 && a.p_planes != nullptr) {
       const int n = (int)(plane / C);
@@ -573,7 +574,7 @@ __global__ void __launch_bounds__(256) k_bn1_relu_pool_planes(BnPoolArgs a) {
       v1 = rnd<T>((v1 - mu) * is * gm + b);
       v2 = rnd<T>((v2 - mu) * is * gm + b);
       v3 = rnd<T>((v3 - mu) * is * gm + b);
-      o[j] = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
+      o[j] = relu_max4(v0, v1, v2, v3);
     }
     T* dst = pl + (((n * 2 + g) * 320 + (ph + 3) * 16 + pw) * 8);
     store4<T>(dst, o[0], o[1], o[2], o[3]);
@@ -784,7 +785,7 @@ __global__ void __launch_bounds__(224, NI == 4 ? 2 : 1) k_fc_ce(FcArgs a) {  // 
       const float mu = s_bn[c][0], is = s_bn[c][1], gm = s_bn[c][2], bt = s_bn[c][3];
       const float v0 = rnd<T>((yw[i][0] - mu) * is * gm + bt), v1 = rnd<T>((yw[i][1] - mu) * is * gm + bt);
       const float v2 = rnd<T>((yw[i][2] - mu) * is * gm + bt), v3 = rnd<T>((yw[i][3] - mu) * is * gm + bt);
-      pooled[i] = fmaxf(fmaxf(fmaxf(v0, v1), fmaxf(v2, v3)), 0.f);
+      pooled[i] = relu_max4(v0, v1, v2, v3);
       stf<T>(&p2w[(size_t)blockIdx.x * 1568 + k], pooled[i]);
     }
   } else if (fuse && tid < 128) {  // the first two were written by the predecessor

@@ -39,12 +39,10 @@ struct StepArgs {
   int B;
   int rows_conv1, rows_conv2w, rows_conv2b, rows_fc;
   int use_scaler, sync;
-  float lr, growth_factor, backoff_factor;
+  float growth_factor, backoff_factor;
   int growth_interval;
-  // the other torch.optim.SGD knobs (sgd.py:425-465); all zero for the reference
+  // lr and the other torch.optim.SGD knobs (sgd.py:425-465) are read from DevState: run-time state, see common.cuh
   float* mom;  // [N_PAD] momentum buffers
-  float momentum, weight_decay, dampening;
-  int nesterov;
 };
 
 // conv2's filter is kept, besides its fp32 master copy, as ready-made tcgen05 B operands
@@ -96,6 +94,8 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   const float scale = a.ds->scale;
   const int tracker = a.ds->growth_tracker;
   const int mom_ready = a.ds->mom_ready;
+  const float lr = a.ds->lr, momentum = a.ds->momentum, weight_decay = a.ds->weight_decay, dampening = a.ds->dampening;
+  const int nesterov = a.ds->nesterov;
   if (tid == 0) s_nonfinite = 0;
   // parameters are fetched now, long before they are needed, so the load overlaps everything below
   float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -105,6 +105,8 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   }
   pdl_sync();  // predecessor: conv1 weight gradient (the side branches are joined by full dependencies)
   if (threadIdx.x == 0) TRACE(13 * 16 + 1);
+  // a cross-rank wait of an earlier kernel of this step (or of an earlier step) timed out: bit 1 of the cluster-wide flag
+  const int err_before = *reinterpret_cast<volatile int*>(&a.ds->error);
   // CTA 0 owns the conv1 region (elements 0..415), whose gradient arrives as one partial row per
   // conv1-wgrad CTA: all 1024 threads sum it together (9 row lanes per float4, one round trip to
   // L2 instead of rows/8), fixed order.  Warp 0 also fetches the per-image losses now.
@@ -205,9 +207,13 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
                                 __uint_as_float(reinterpret_cast<const unsigned int*>(a.nbt)[tid]), tag);
         }
       } else {
-        if (tid < N_BNBUF) a.bnbuf[tid] = ll_wait(&a.comm.self->ll_bnbuf[tid], tag, &a.ds->error);
-        if (tid < 4) reinterpret_cast<unsigned int*>(a.nbt)[tid] =
-            __float_as_uint(ll_wait(&a.comm.self->ll_bnbuf[N_BNBUF + tid], tag, &a.ds->error));
+        float bv = 0.f, nv = 0.f;
+        if (tid < N_BNBUF) bv = ll_wait(&a.comm.self->ll_bnbuf[tid], tag, a.ds);
+        if (tid < 4) nv = ll_wait(&a.comm.self->ll_bnbuf[N_BNBUF + tid], tag, a.ds);
+        if (*reinterpret_cast<volatile int*>(&a.ds->error) == 0) {  // never adopt words of a timed-out wait
+          if (tid < N_BNBUF) a.bnbuf[tid] = bv;
+          if (tid < 4) reinterpret_cast<unsigned int*>(a.nbt)[tid] = __float_as_uint(nv);
+        }
       }
     }
     if (valid) {
@@ -220,7 +226,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
       for (int half = 0; half < 2; ++half) {  // two gathers of four senders keep the 1024-thread CTA within 64 registers
         if (half * 4 < W) {
           float got[16];
-          ll_gather<4, 4>(&a.comm.self->ll_inbox[par][0][e], N_PAD, idx, half * 4, W, tag, got, &a.ds->error);
+          if (!ll_gather<4, 4>(&a.comm.self->ll_inbox[par][0][e], N_PAD, idx, half * 4, W, tag, got, a.ds)) atomicOr(&s_nonfinite, 2);
 #pragma unroll
           for (int q = 0; q < 4; ++q)  // fixed rank order
             if (half * 4 + q < W) { tot.x += got[q * 4]; tot.y += got[q * 4 + 1]; tot.z += got[q * 4 + 2]; tot.w += got[q * 4 + 3]; }
@@ -238,6 +244,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     const bool bad = !(isfinite(u.x) && isfinite(u.y) && isfinite(u.z) && isfinite(u.w));
     if (valid && bad) atomicOr(&s_nonfinite, 1);
   }
+  if (err_before != 0 && tid == 0) atomicOr(&s_nonfinite, 2);
   // ---- 4. cluster-wide found_inf through distributed shared memory: every CTA writes its flag into
   // slot [its rank] of ALL eight CTAs (the cluster is co-scheduled, so remote shared memory exists
   // from the start), ONE cluster barrier, then everybody reads its own eight slots
@@ -245,9 +252,13 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   if (tid < STEP_CTAS) *cluster.map_shared_rank(&s_flags[cta], tid) = s_nonfinite;
   cluster.sync();
   if (threadIdx.x == 0) TRACE(13 * 16 + 4);
-  int found = 0;
+  int flags = 0;
 #pragma unroll
-  for (int r = 0; r < STEP_CTAS; ++r) found |= s_flags[r];
+  for (int r = 0; r < STEP_CTAS; ++r) flags |= s_flags[r];
+  // bit 1: a peer did not answer in time somewhere in this step.  The gradient is then not the all-reduced one: the
+  // step applies NOTHING (parameters, momentum, scaler state stay as they were) and tells the host (DDPSTEP_E_PEER).
+  const bool dead = (flags & 2) != 0;
+  const int found = (flags & 1) | (dead ? 1 : 0);
 
   // the gradient taps are stored only now: a release at cluster scope waits for every global
   // store issued before it, so none may be in flight while the barrier above runs
@@ -265,31 +276,31 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   // ---- 5. SGD (skipped on overflow), same expression as _foreach_add_(p, g, alpha=-lr)
   if (valid && !found) {
     float4 p = p4;
-    if (a.weight_decay != 0.f) {  // _foreach_add(grads, params, alpha=weight_decay): a new tensor, .grad stays as it was
-      u.x = fmaf(a.weight_decay, p.x, u.x); u.y = fmaf(a.weight_decay, p.y, u.y);
-      u.z = fmaf(a.weight_decay, p.z, u.z); u.w = fmaf(a.weight_decay, p.w, u.w);
+    if (weight_decay != 0.f) {  // _foreach_add(grads, params, alpha=weight_decay): a new tensor, .grad stays as it was
+      u.x = fmaf(weight_decay, p.x, u.x); u.y = fmaf(weight_decay, p.y, u.y);
+      u.z = fmaf(weight_decay, p.z, u.z); u.w = fmaf(weight_decay, p.w, u.w);
     }
-    if (a.momentum != 0.f) {
+    if (momentum != 0.f) {
       float4 b = u;  // first executed step: buf = clone(grad)
       if (mom_ready) {  // _foreach_mul_(bufs, momentum); _foreach_add_(bufs, grads, alpha=1 - dampening)
         b = make_float4(0.f, 0.f, 0.f, 0.f);
         if (e + 4 <= N_PARAM) b = *reinterpret_cast<const float4*>(a.mom + e);
         else { b.x = a.mom[e]; b.y = a.mom[e + 1]; }
-        const float k = 1.0f - a.dampening;
-        b.x = fmaf(k, u.x, b.x * a.momentum); b.y = fmaf(k, u.y, b.y * a.momentum);
-        b.z = fmaf(k, u.z, b.z * a.momentum); b.w = fmaf(k, u.w, b.w * a.momentum);
+        const float k = 1.0f - dampening;
+        b.x = fmaf(k, u.x, b.x * momentum); b.y = fmaf(k, u.y, b.y * momentum);
+        b.z = fmaf(k, u.z, b.z * momentum); b.w = fmaf(k, u.w, b.w * momentum);
       }
       if (e + 4 <= N_PARAM) *reinterpret_cast<float4*>(a.mom + e) = b;
       else { a.mom[e] = b.x; a.mom[e + 1] = b.y; }
-      if (a.nesterov) {  // _foreach_add_(grads, bufs, alpha=momentum)
-        u.x = fmaf(a.momentum, b.x, u.x); u.y = fmaf(a.momentum, b.y, u.y);
-        u.z = fmaf(a.momentum, b.z, u.z); u.w = fmaf(a.momentum, b.w, u.w);
+      if (nesterov) {  // _foreach_add_(grads, bufs, alpha=momentum)
+        u.x = fmaf(momentum, b.x, u.x); u.y = fmaf(momentum, b.y, u.y);
+        u.z = fmaf(momentum, b.z, u.z); u.w = fmaf(momentum, b.w, u.w);
       } else {
         u = b;
       }
     }
-    p.x = fmaf(-a.lr, u.x, p.x); p.y = fmaf(-a.lr, u.y, p.y);
-    p.z = fmaf(-a.lr, u.z, p.z); p.w = fmaf(-a.lr, u.w, p.w);
+    p.x = fmaf(-lr, u.x, p.x); p.y = fmaf(-lr, u.y, p.y);
+    p.z = fmaf(-lr, u.z, p.z); p.w = fmaf(-lr, u.w, p.w);
     if (e + 4 <= N_PARAM) {
       *reinterpret_cast<float4*>(a.params + e) = p;
     } else {
@@ -305,7 +316,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     if (tid == 0) {
       a.ds->loss = rnd<T>(s / (float)a.B);
       a.ds->found_inf = found ? 1.0f : 0.0f;
-      if (a.use_scaler) {
+      if (a.use_scaler && !dead) {
         if (found) {
           a.ds->scale = scale * a.backoff_factor;
           a.ds->growth_tracker = 0;
@@ -320,10 +331,11 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
           }
         }
       }
-      if (!found && a.momentum != 0.f) a.ds->mom_ready = 1;
+      if (!found && momentum != 0.f) a.ds->mom_ready = 1;
       a.ds->epoch = epoch + 1ull;
       if (a.host_mail != nullptr) {
         a.host_mail[0] = rnd<T>(s / (float)a.B);
+        if (dead) reinterpret_cast<volatile int*>(a.host_mail)[2] = 1;  // sticky: the host API refuses further steps
         __threadfence_system();
         reinterpret_cast<volatile unsigned int*>(a.host_mail)[1] = (unsigned int)epoch + 1u;
       }
@@ -346,14 +358,14 @@ __global__ void k_reduce_counts(CountsArgs a) {
   if (W > 1) {
     if (tid == 0) {
       // the slot is single-buffered: rank 0 must have consumed our previous push
-      if (ep > 0) wait_flag(&a.comm.self->flag_counts_ack, ep, &a.ds->error);
+      if (ep > 0) wait_flag(&a.comm.self->flag_counts_ack, ep, a.ds);
       a.comm.peer[0]->slot_counts[rank][0] = a.counts[0];
       a.comm.peer[0]->slot_counts[rank][1] = a.counts[1];
       __threadfence_system();
       st_release_sys(&a.comm.peer[0]->flag_counts[rank], ep + 1ull);
     }
     if (rank == 0) {
-      if (tid < W) wait_flag(&a.comm.self->flag_counts[tid], ep + 1ull, &a.ds->error);
+      if (tid < W) wait_flag(&a.comm.self->flag_counts[tid], ep + 1ull, a.ds);
       __syncthreads();
       if (tid < 2) {
         float s = 0.f;

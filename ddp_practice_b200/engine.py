@@ -215,6 +215,18 @@ class Engine:
             i += 1
         return out
 
+    def set_sgd(self, lr: float, momentum: float = 0.0, weight_decay: float = 0.0, dampening: float = 0.0,
+                nesterov: bool = False):
+        """`optimizer.param_groups[0]` changed (LR scheduler): new values for the steps enqueued from now on."""
+        self._check(self.lib.ddpstep_set_sgd(self.ctx, lr, momentum, weight_decay, dampening, int(nesterov), self._stream()))
+
+    def set_peer_timeout_ms(self, ms: float):
+        self._check(self.lib.ddpstep_set_peer_timeout_ms(self.ctx, float(ms)))
+
+    def allreduce_only(self):
+        """The tail kernel alone (all-reduce + unscale + SGD + scale update) on the last step's partial gradients."""
+        self._check(self.lib.ddpstep_allreduce_only(self.ctx, self._stream()))
+
     def launch_count(self) -> int:
         return int(self.lib.ddpstep_launch_count(self.ctx))
 

@@ -123,12 +123,14 @@ class DistributedDataParallel(_tnn.Module):
                 for t in list(module.parameters()) + list(module.buffers()):
                     dist.broadcast(t.data, 0)
         self.amp_dtype = self._probe_dtype()
-        self.batch_cap = int(os.environ.get("DDP_B200_BATCH_CAP", "4096"))
+        self.batch_cap = 0
+        self._scaler_cfg = None
         self.engine: Optional[Engine] = None
         self._engine_key = None
         self._armed = None
         self._steps = 0
         self._mom_published = False  # optimizer.state[p]['momentum_buffer'] views handed out
+        self._optimizer = None       # the optimizer seen by the last step (its state holds views of our memory)
         self.last_logits = None
 
     # -- construction helpers -------------------------------------------------------------
@@ -151,34 +153,75 @@ class DistributedDataParallel(_tnn.Module):
         sd_b = dict(self.module.named_buffers())
         return sd_p, sd_b
 
-    def _ensure_engine(self, use_scaler: bool, lr: float = 1e-4, scaler: "GradScaler" = None, sgd: dict = None):
+    def _ensure_engine(self, use_scaler: bool, lr: float = 1e-4, scaler: "GradScaler" = None, sgd: dict = None,
+                       batch: int = 0):
+        """The native context is built at the first step (or first eval).  What may change afterwards -- lr and the
+        other SGD knobs of `optimizer.param_groups[0]`, e.g. under an LR scheduler -- is run-time state of the
+        library (`ddpstep_set_sgd`): no new context, no IPC re-exchange, no graph re-capture, and the live
+        GradScaler state is never touched.  Only a batch larger than any seen so far, or a GradScaler whose
+        constructor arguments differ from what an eval-first context assumed, rebuild it -- carrying every piece of
+        live state (parameters, BN buffers, scale, growth tracker, momentum buffers) over."""
         sgd = sgd or {}
-        key = (use_scaler, float(lr), tuple(sorted(sgd.items())))
-        if self.engine is not None and self._engine_key == key:
-            return self.engine
+        hyper = (float(lr), tuple(sorted(sgd.items())))
+        scfg = None if scaler is None else (scaler._growth_factor, scaler._backoff_factor, scaler._growth_interval)
+        carry = None
+        if self.engine is not None:
+            if self._steps > 0 and use_scaler != self._engine_key[0]:
+                raise RuntimeError("one model cannot mix scaler.step(optimizer) and optimizer.step(): the native "
+                                   "context is built for one of the two (ddp_main.py:91-93 vs origin_main.py:64-66)")
+            rebuild = batch > self.engine.batch_cap or use_scaler != self._engine_key[0]
+            rebuild = rebuild or (scfg is not None and self._scaler_cfg is not None and scfg != self._scaler_cfg)
+            if not rebuild:
+                if scfg is not None and self._scaler_cfg is None:  # eval-first context, scaler defaults matched
+                    self._scaler_cfg = scfg
+                    if scaler._loaded or scaler._init_scale != 65536.0:
+                        self.engine.set_scaler(scaler._init_scale_now(), scaler._tracker_now())
+                if hyper != self._engine_key[1]:
+                    self.engine.set_sgd(float(lr), float(sgd.get("momentum", 0.0)), float(sgd.get("weight_decay", 0.0)),
+                                        float(sgd.get("dampening", 0.0)), bool(sgd.get("nesterov", False)))
+                    self._engine_key = (use_scaler, hyper)
+                return self.engine
+            old = self.engine
+            old.check_device()
+            carry = {"scale": float(old.scale.item()), "tracker": int(old.growth_tracker.item()),
+                     "mom": old.momentum_buffer.clone() if int(old.momentum_ready.item()) else None,
+                     "stepped": self._steps > 0}
+            opt = self._optimizer
+            if opt is not None:  # its momentum_buffer entries are views of the context about to be freed
+                lo = old.momentum_buffer.data_ptr()
+                for st in opt.state.values():
+                    buf = st.get("momentum_buffer")
+                    if buf is not None and lo <= buf.data_ptr() < lo + 4 * old.momentum_buffer.numel():
+                        del st["momentum_buffer"]
+        key = (use_scaler, hyper)
         sd_p, sd_b = self._named()
         flat = torch.cat([sd_p[n].detach().reshape(-1).float() for n, _ in _SPECS]).cpu()
         bn = torch.cat([sd_b[n].detach().float() for n, _, _ in _BUFS]).cpu()
         nbt = [int(sd_b["layer1.1.num_batches_tracked"]), int(sd_b["layer2.1.num_batches_tracked"])]
+        if carry is not None:
+            self.engine.close()
+            self.engine = None
         kw = {}
         if scaler is not None:
             kw = dict(init_scale=scaler._init_scale_now(), growth_factor=scaler._growth_factor,
                       backoff_factor=scaler._backoff_factor, growth_interval=scaler._growth_interval)
         tracker = scaler._tracker_now() if scaler is not None else 0
-        mom = None
-        if self.engine is not None:
-            if int(self.engine.momentum_ready.item()):  # a changed hyper-parameter rebuilds the context: keep the buffers
-                mom = self.engine.momentum_buffer.clone()
-            self.engine.close()
-        eng = Engine(dtype=self.amp_dtype, batch_cap=self.batch_cap, rank=self.rank, world=self.world,
+        # sized for the batches actually seen (ddp_main.py:51 `-b`, default 32), not for the largest one imaginable;
+        # DDP_B200_BATCH_CAP pre-sizes it
+        cap = max(int(os.environ.get("DDP_B200_BATCH_CAP", "0")), int(batch), self.batch_cap, 32)
+        self.batch_cap = cap
+        eng = Engine(dtype=self.amp_dtype, batch_cap=cap, rank=self.rank, world=self.world,
                      device=self.device_index, use_scaler=use_scaler, sync_bn=self.sync_bn, lr=lr, **kw, **sgd)
         eng.connect()
         eng.load_state(flat.numpy(), bn.numpy(), nbt)
-        if mom is not None:
-            eng.momentum_buffer.copy_(mom)
-            eng.momentum_ready.fill_(1)
-        if scaler is not None and tracker:
+        if carry is not None and carry["stepped"] and use_scaler:
+            eng.set_scaler(carry["scale"], carry["tracker"])  # the LIVE scaler state, not the constructor's
+        elif scaler is not None and tracker:
             eng.set_scaler(kw["init_scale"], tracker)
+        if carry is not None and carry["mom"] is not None:
+            eng.momentum_buffer.copy_(carry["mom"])
+            eng.momentum_ready.fill_(1)
+        self._scaler_cfg = scfg
         # re-point the module's tensors at the library's memory: state_dict(), parameters(),
         # torch.save and p.grad keep working and always show the live values
         off = 0
@@ -194,7 +237,22 @@ class DistributedDataParallel(_tnn.Module):
         sd_b["layer1.1.num_batches_tracked"].data = eng.num_batches_tracked[0]
         sd_b["layer2.1.num_batches_tracked"].data = eng.num_batches_tracked[1]
         self.engine, self._engine_key = eng, key
+        if carry is not None:
+            self._mom_published = False  # optimizer.state views point into the old context: re-publish
         return eng
+
+    # -- failure reporting ----------------------------------------------------------------
+    def state_dict(self, *a, **k):
+        """`model.state_dict()` (ddp_main.py:166): the tensors alias the library's memory, so first make sure no
+        step was voided by a peer timeout (raises NativeError / DDPSTEP_E_PEER otherwise)."""
+        if self.engine is not None:
+            self.engine.check_device()
+        return super().state_dict(*a, **k)
+
+    def train(self, mode: bool = True):
+        if self.engine is not None and not mode:  # entering test() (ddp_main.py:98): once per epoch
+            self.engine.check_device()
+        return super().train(mode)
 
     def _attach_grads(self):
         sd_p, _ = self._named()
@@ -210,7 +268,10 @@ class DistributedDataParallel(_tnn.Module):
         images = images.contiguous().float()
         if self.training:
             return _Pending(self, images)  # ddp_main.py:88
-        eng = self.engine or self._ensure_engine(use_scaler=self.amp_dtype != "fp32")
+        eng = self.engine
+        if eng is None or images.shape[0] > eng.batch_cap:
+            key = self._engine_key or (self.amp_dtype != "fp32", (1e-4, ()))
+            eng = self._ensure_engine(key[0], key[1][0], None, dict(key[1][1]), batch=images.shape[0])
         return eng.eval_batch(images)  # ddp_main.py:104: real logits tensor
 
     def _arm(self, loss: _Loss, scaled: bool):
@@ -241,7 +302,8 @@ class DistributedDataParallel(_tnn.Module):
         if scaled != use_scaler:
             raise RuntimeError("scaler.scale(loss).backward() must be followed by scaler.step(optimizer), and "
                                "loss.backward() by optimizer.step()")
-        eng = self._ensure_engine(use_scaler, lr, scaler, sgd)
+        self._optimizer = optimizer
+        eng = self._ensure_engine(use_scaler, lr, scaler, sgd, batch=loss.images.shape[0])
         momentum = bool(sgd and sgd.get("momentum", 0.0) != 0.0 and optimizer is not None)
         if momentum and optimizer.state:
             # cheap sentinel: only a load_state_dict() since the last step makes the first buffer something else

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define DDPSTEP_ABI_VERSION 2
+#define DDPSTEP_ABI_VERSION 3
 
 #define DDPSTEP_N_PARAMS 29034   /* flat fp32 parameter / gradient bucket length   */
 #define DDPSTEP_N_BNBUF 96       /* rm1[16] rv1[16] rm2[32] rv2[32]                */
@@ -35,7 +35,8 @@ enum {
   DDPSTEP_E_ARG = -1,      /* bad argument (batch > batch_cap, world > 8, null pointer ...) */
   DDPSTEP_E_CUDA = -2,     /* a CUDA runtime call failed                                    */
   DDPSTEP_E_STATE = -3,    /* call out of order (e.g. step before peers were imported)      */
-  DDPSTEP_E_PEER = -4,     /* a peer did not answer within the spin timeout                 */
+  DDPSTEP_E_PEER = -4,     /* a peer did not answer within the timeout: the affected step and all
+                              later ones applied no update; the context refuses further steps */
   DDPSTEP_E_ARCH = -5      /* device is not sm_100                                          */
 };
 
@@ -178,6 +179,9 @@ const char* ddpstep_kernel_name(int32_t i);   /* names of those kernels, "" past
  * is caller-owned device memory: params_dev = the first 416 floats of the flat parameter
  * vector (conv1 weight[400], bias[16]); x_dev = [batch,1,28,28] fp32; y1_dev = [batch,16,28,28]
  * in `dtype`; stats_dev = 32 floats, mean[16] then 1/sqrt(biased var + bn_eps)[16].
+ * Alignment: x_dev and y1_dev 16 bytes (the kernel uses 16-byte loads and 8/16-byte stores),
+ * params_dev and stats_dev 4 bytes; anything else is refused with DDPSTEP_E_ARG rather than
+ * faulting inside the caller's CUDA context.
  * Limit: batch <= 1024 (DDPSTEP_E_ARG beyond it, text via ddpstep_last_error(NULL)): the
  * kernel's scratch -- a row of partial sums per image -- is a fixed array of about 130 KB
  * inside the library, resident on every GPU that loads it until the process exits.
@@ -189,9 +193,29 @@ const char* ddpstep_kernel_name(int32_t i);   /* names of those kernels, "" past
 int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const float* x_dev, int32_t batch, int32_t dtype,
                                   int32_t conv_bias_double_round, float bn_eps, void* y1_dev, float* stats_dev,
                                   void* stream);
+/* `optimizer.param_groups[0]` at run time -- an LR scheduler's step, or the group edited by hand
+ * (torch/optim/sgd.py:425-465 reads lr / momentum / weight_decay / dampening / nesterov from the
+ * group on every optimizer.step(); ddp_main.py:125 sets them once).  The values live in device
+ * memory, so neither the context nor its captured graphs are rebuilt.  Stream-ordered: steps
+ * enqueued on `stream` after this call use the new values.                                    */
+int ddpstep_set_sgd(ddpstep_ctx* ctx, float lr, float momentum, float weight_decay, float dampening,
+                    int32_t nesterov, void* stream);
+/* How long a kernel polls for a peer's words before giving up (default 20 s; environment
+ * DDPSTEP_PEER_TIMEOUT_MS at create time).  The reference's NCCL blocks until its watchdog
+ * fires; here the step whose wait expired applies no update and this and
+ * every later step entry point returns DDPSTEP_E_PEER.                                        */
+int ddpstep_set_peer_timeout_ms(ddpstep_ctx* ctx, double ms);
+/* The Reducer all-reduce of the one 116,136-byte bucket with everything fused behind it
+ * (ncclAllReduce of reducer.hpp:524 behind ddp_main.py:121-123, then grad_scaler.py:294-298,371
+ * and sgd.py:473) launched ALONE: the tail kernel re-reduces the partial gradients the last
+ * training step left behind (state advances as for a step).  Exists so that the exchange can be
+ * timed in isolation against ncclAllReduce (tools/allreduce_bench.py, bench.py `allreduce`);
+ * collective: every rank calls it the same number of times.                                   */
+int ddpstep_allreduce_only(ddpstep_ctx* ctx, void* stream);
 /* Number of kernel launches (graph kernel nodes count one each) issued so far.             */
 int64_t ddpstep_launch_count(const ddpstep_ctx* ctx);
-/* Device-side error word (peer timeout etc.), 0 = healthy.  Synchronises the device.       */
+/* Device-side error word (peer timeout), 0 = healthy.  Synchronises the device.  The step
+ * entry points report the same condition without synchronising, one or two steps late.      */
 int ddpstep_device_status(ddpstep_ctx* ctx);
 
 #ifdef __cplusplus

@@ -93,7 +93,7 @@ def test_step_matches_oracle(dtype, batch):
 
 
 @pytest.mark.parametrize("dtype,batch", [("fp16", 1), ("fp16", 2), ("fp16", 63), ("fp16", 64), ("fp16", 65), ("fp16", 130),
-                                         ("fp16", 300), ("bf16", 65), ("fp32", 1), ("fp32", 65)])
+                                         ("fp16", 300), ("bf16", 65), ("fp32", 1), ("fp32", 65), ("fp32", 300)])
 def test_batch_size_boundaries_match_oracle(dtype, batch):
     """Edges of the kernel selection: a single image, the last batch that uses the small-batch kernels (64: conv1 on
     CUDA cores, tagged partial rows, fused tile refresh / BN2 pass 1), the first that does not (65: tcgen05 conv1,
@@ -369,6 +369,62 @@ def test_sgd_momentum_weight_decay_nesterov_match_torch_on_the_same_gradients(dt
         if kw.get("momentum"):
             assert e.momentum_ready.item() == 1
             assert torch.equal(e.momentum_buffer.view(torch.int32), opt.state[p_ref]["momentum_buffer"].view(torch.int32))
+    e.close()
+
+
+def test_lr_schedule_changes_run_time_state_not_the_context():
+    """an LR scheduler must not rebuild anything.  `ddpstep_set_sgd` changes lr (and the other knobs) between
+    steps; parameters keep matching torch.optim.SGD bit for bit, the GradScaler state keeps its own trajectory, and the
+    launch count shows the same captured graph being replayed."""
+    st = _seed_state()
+    e = _engine(dtype="fp16", batch_cap=32, lr=1e-3, momentum=0.9)
+    e.load_state(st.flat_params().numpy(), _bn_of(st))
+    p_ref = torch.nn.Parameter(e.params.clone())
+    opt = torch.optim.SGD([p_ref], lr=1e-3, momentum=0.9)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=1, gamma=0.5)
+    x, y = O.synthetic_mnist(32 * 6)
+    trackers = []
+    for s in range(6):
+        e.train_step(x[s * 32:(s + 1) * 32].cuda().contiguous(), y[s * 32:(s + 1) * 32].cuda().contiguous())
+        torch.cuda.synchronize()
+        trackers.append(e.growth_tracker.item())
+        if e.found_inf.item() == 0.0:
+            p_ref.grad = e.grads.clone()
+            opt.step()
+            sched.step()
+            e.set_sgd(opt.param_groups[0]["lr"], momentum=0.9)
+            assert torch.equal(e.params.view(torch.int32), p_ref.detach().view(torch.int32)), f"step {s}"
+    assert trackers == [0, 1, 2, 3, 4, 5] and e.scale.item() == 32768.0
+    assert e.launch_count() == 12 * 6
+    e.close()
+
+
+def test_nan_input_poisons_the_step_like_torch():
+    """a NaN pixel.  In torch it propagates through conv / BN (the batch statistics become NaN) /
+    ReLU / max-pool into the loss and every gradient, `found_inf` is raised and the step is skipped.  The decision
+    (found_inf, scale halved, parameters untouched) must be the same here."""
+    torch.manual_seed(3407)
+    model = RefConvNet(torch.float16, "cuda").cuda()
+    tr = RefTrainer(model, True)
+    e = _engine(dtype="fp16", batch_cap=32)
+    e.load_state(flat_params(model).numpy(), bn_buffers(model).numpy())
+    x, y = O.synthetic_mnist(64)
+    x, y = x.cuda(), y.cuda()
+    ref0 = tr.step(x[:32].contiguous(), y[:32].contiguous())   # step 0: the fp16 overflow step on both sides
+    e.train_step(x[:32].contiguous(), y[:32].contiguous())
+    xs = x[32:].clone().contiguous()
+    xs[3, 0, 10, 10] = float("nan")
+    p0 = e.params.clone()
+    ref = tr.step(xs, y[32:].contiguous())
+    e.train_step(xs, y[32:].contiguous())
+    torch.cuda.synchronize()
+    assert ref0["found_inf"] == 1.0 and ref["found_inf"] == 1.0
+    assert e.found_inf.item() == 1.0
+    # the NaN reaches the loss on both sides: ReLU and max-pool propagate it (relu_max4), they do not drop it
+    assert ref["loss"] != ref["loss"] and e.loss.item() != e.loss.item()
+    assert (e.scale.item(), e.growth_tracker.item()) == (ref["scale"], ref["tracker"]) == (16384.0, 0)
+    assert torch.equal(p0, e.params)
+    assert not torch.isfinite(e.grads_scaled).all()
     e.close()
 
 

@@ -112,4 +112,4 @@ def test_config_struct_mirrors_the_header():
     assert fields("ddpstep_ptrs") == [n for n, _ in _lib.Ptrs._fields_]
     cfg = _lib.Config()
     _lib.load().ddpstep_default_config(cfg)
-    assert cfg.abi_version == 2 and cfg.momentum == 0.0 and cfg.nesterov == 0 and abs(cfg.lr - 1e-4) < 1e-10
+    assert cfg.abi_version == 3 and cfg.momentum == 0.0 and cfg.nesterov == 0 and abs(cfg.lr - 1e-4) < 1e-10

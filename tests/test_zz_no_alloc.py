@@ -35,7 +35,8 @@ def _call(lib, params, x, dtype_id, tdt, eps=1e-5):
     return y1, stats
 
 
-@pytest.mark.parametrize("dtype,dtype_id,tdt", [("fp16", 1, torch.float16), ("fp32", 0, torch.float32)])
+@pytest.mark.parametrize("dtype,dtype_id,tdt", [("fp16", 1, torch.float16), ("fp32", 0, torch.float32),
+                                                ("bf16", 2, torch.bfloat16)])
 def test_no_alloc_entry_point_matches_context_path_twice_in_a_row(dtype, dtype_id, tdt):
     from ddp_practice_b200 import Engine, _lib
     lib = _lib.load()
@@ -64,6 +65,53 @@ def test_no_alloc_entry_point_matches_context_path_twice_in_a_row(dtype, dtype_i
         m_ref, is_ref, _ = O._local_stats(y1_ref)
         assert torch.allclose(mean, m_ref, rtol=1e-5, atol=1e-7)
         assert torch.allclose(invstd, is_ref, rtol=1e-5)
+
+
+@pytest.mark.parametrize("dtype,dtype_id,tdt", [("fp16", 1, torch.float16), ("bf16", 2, torch.bfloat16)])
+def test_no_alloc_entry_point_large_batches_up_to_the_limit(dtype, dtype_id, tdt, monkeypatch):
+    """Above 296 images this entry point launches one CTA per image (one partial row each, up to the 1024 rows of the
+    fixed scratch) while a context grid-strides over 296 CTAs: 300 images, then the limit itself, 1024, in a row.
+    The context is told to run conv1 with the same CUDA-core kernel (DDPSTEP_CONV1_TC=0; its default above 64 images is
+    the tensor-core kernel), so the conv output must agree bit for bit; the statistics are sums in a different order
+    and are compared at 1e-5."""
+    from ddp_practice_b200 import Engine, _lib
+    monkeypatch.setenv("DDPSTEP_CONV1_TC", "0")
+    lib = _lib.load()
+    torch.manual_seed(3407)
+    st = O.OracleState.from_state_dict(RefConvNet(None, "cpu").state_dict())
+    bn = torch.cat([st.running_mean[0], st.running_var[0], st.running_mean[1], st.running_var[1]]).numpy()
+    x, y = O.synthetic_mnist(300 + 1024, seed=78)
+    params = st.flat_params().cuda()
+    eng = Engine(dtype=dtype, batch_cap=1024)
+    for lo, hi in ((0, 300), (300, 1324)):
+        xs, ys = x[lo:hi].cuda().contiguous(), y[lo:hi].cuda().contiguous()
+        n = hi - lo
+        eng.load_state(st.flat_params().numpy(), bn)
+        eng.train_step(xs, ys)
+        torch.cuda.synchronize()
+        y1_ref = eng.read_activation("y1", n)
+        y1, stats = _call(lib, params, xs, dtype_id, tdt)
+        assert torch.equal(y1.float().cpu(), y1_ref), f"conv1 output differs (batch {n})"
+        m_ref, is_ref, _ = O._local_stats(y1_ref)
+        assert torch.allclose(stats[:16].cpu(), m_ref, rtol=1e-5, atol=1e-6)
+        assert torch.allclose(stats[16:].cpu(), is_ref, rtol=1e-5)
+    eng.close()
+
+
+def test_no_alloc_entry_point_rejects_misaligned_buffers():
+    """A caller carving buffers out of its own arena may hand over an odd offset: refused up front (the kernel's 16-byte
+    accesses would otherwise raise a sticky fault in the caller's CUDA context)."""
+    from ddp_practice_b200 import _lib
+    lib = _lib.load()
+    p = torch.zeros(416, device="cuda")
+    x = torch.zeros(8 * 784 + 4, device="cuda")
+    y1 = torch.zeros(8 * 16 * 784 + 4, device="cuda")
+    out = torch.zeros(32, device="cuda")
+    rc = lib.ddpstep_conv1_bnstats_noalloc(p.data_ptr(), x.data_ptr() + 4, 8, 0, 1, 1e-5, y1.data_ptr(), out.data_ptr(), None)
+    assert rc == -1 and b"aligned" in lib.ddpstep_last_error(None)
+    rc = lib.ddpstep_conv1_bnstats_noalloc(p.data_ptr(), x.data_ptr(), 8, 0, 1, 1e-5, y1.data_ptr() + 8, out.data_ptr(), None)
+    assert rc == -1 and b"aligned" in lib.ddpstep_last_error(None)
+    torch.cuda.synchronize()  # nothing was launched, nothing faulted
 
 
 def test_no_alloc_entry_point_rejects_oversize_batch():
