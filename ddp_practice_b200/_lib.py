@@ -43,6 +43,7 @@ SYMBOLS = [
     ("ddpstep_set_scaler", C.c_int, [_P, C.c_float, C.c_int32]),
     ("ddpstep_state_ptrs", C.c_int, [_P, C.POINTER(Ptrs)]),
     ("ddpstep_train_step", C.c_int, [_P, _P, _P, C.c_int32, _P]),
+    ("ddpstep_train_step_accumulate", C.c_int, [_P, _P, _P, C.c_int32, _P]),
     ("ddpstep_train_step_host", C.c_int, [_P, _P, _P, C.c_int32, _P, _P]),
     ("ddpstep_train_step_indexed", C.c_int, [_P, _P, _P, _P, C.c_int32, _P]),
     ("ddpstep_eval_batch_indexed", C.c_int, [_P, _P, _P, _P, C.c_int32, _P]),
@@ -57,6 +58,7 @@ SYMBOLS = [
     ("ddpstep_set_sgd", C.c_int, [_P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int32, _P]),
     ("ddpstep_set_peer_timeout_ms", C.c_int, [_P, C.c_double]),
     ("ddpstep_allreduce_only", C.c_int, [_P, _P]),
+    ("ddpstep_allreduce_bucket", C.c_int, [_P, _P, C.c_int64, C.c_int32, _P]),
     ("ddpstep_launch_count", C.c_int64, [_P]),
     ("ddpstep_device_status", C.c_int, [_P]),
 ]

@@ -25,7 +25,7 @@ using namespace dstep;
 
 static thread_local std::string g_create_error;
 
-// mode: 0 train, 1 eval; source: 0 float batch on the device, 1 uint8 dataset + indices, 2 pinned host batch
+// mode: 0 train, 1 eval, 2 train micro-step inside no_sync(); source: 0 float batch on the device, 1 uint8 dataset + indices, 2 pinned host batch
 typedef std::tuple<int, int, int, int> GraphKey;  // (mode, source, has_labels, batch)
 
 struct GraphEntry {
@@ -88,13 +88,19 @@ struct ddpstep_ctx {
   std::map<GraphKey, GraphEntry> graphs;
   cudaStream_t cap_stream = nullptr, side1 = nullptr, side2 = nullptr;
   cudaEvent_t ev_f0 = nullptr, ev_j0 = nullptr, ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
-  cudaEvent_t ev_h0 = nullptr, ev_h1 = nullptr;
+  cudaEvent_t ev_h0 = nullptr, ev_h1 = nullptr, ev_m = nullptr;
   float* gred = nullptr;
   float* mom = nullptr;   // SGD momentum buffers, same flat layout as the parameters
+  float* acc = nullptr;   // gradient accumulated by DDP.no_sync() micro-steps, same layout
+  bool accumulate = false;  // the step being enqueued is such a micro-step
   volatile float* host_mail = nullptr;  // pinned, mapped: {loss, completed-step counter}
   unsigned int steps_enqueued = 0;     // training steps launched so far (matches DevState.epoch once they finish)
+  bool early_push = true;              // world > 1: side branches push their gradient slices (DDPSTEP_EARLY_PUSH=0: the tail does)
+  bool post_loss = false;              // the step being enqueued posts its loss to the pinned mailbox (host entry point)
   int sm_khz = 1965000;                // SM clock used to turn the peer timeout into clock64() cycles
   StepArgs last_step;                  // arguments of the most recently enqueued tail kernel (ddpstep_allreduce_only)
+  PushArgs last_push_fc, last_push_c2; // ... and of the two early-push kernels (world > 1)
+  int last_c2_ctas = 25;
   int last_step_dtype_ok = 0;
   int cap_bn1 = 0, cap_bn2 = 0, cap_bwd2 = 0, cap_c1w = 0;  // CTAs of the BN consumer kernels the device holds at once (occupancy API)
   int64_t launches = 0;
@@ -172,7 +178,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   A(part1, 296 * 16 * 2 * 4); A(part2, 296 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
   A(part1_ll, 64 * 32 * 8); A(part2_ll, 64 * 64 * 8); A(bpart1_ll, 16 * 64 * 2 * 8); A(bpart2_ll, 32 * 64 * 2 * 8);
   A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
-  A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4); A(mom, N_PAD * 4);
+  A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4); A(mom, N_PAD * 4); A(acc, N_PAD * 4);
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
@@ -184,6 +190,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
     ctx->use_pdl = !(envp && envp[0] == '0');
     const char* envd = getenv("DDPSTEP_DEFER");
     if (envd && envd[0] >= '0' && envd[0] <= '2') ctx->defer_stats = envd[0] - '0';
+    const char* enve = getenv("DDPSTEP_EARLY_PUSH");
+    ctx->early_push = !(enve && enve[0] == '0');
     const char* envm = getenv("DDPSTEP_MID");
     ctx->fuse_mid = envm && envm[0] == '1';
     const char* envh = getenv("DDPSTEP_HEAD");
@@ -218,15 +226,17 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   if (e == cudaSuccess) { void* hm = nullptr; e = cudaHostAlloc(&hm, 64, cudaHostAllocMapped); if (e == cudaSuccess) { memset(hm, 0, 64); ctx->host_mail = static_cast<volatile float*>(hm); } }
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side1, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->side2, cudaStreamNonBlocking);
-  for (cudaEvent_t* ev : {&ctx->ev_f0, &ctx->ev_j0, &ctx->ev_f1, &ctx->ev_j1, &ctx->ev_f2, &ctx->ev_j2, &ctx->ev_h0, &ctx->ev_h1})
+  for (cudaEvent_t* ev : {&ctx->ev_f0, &ctx->ev_j0, &ctx->ev_f1, &ctx->ev_j1, &ctx->ev_f2, &ctx->ev_j2, &ctx->ev_h0, &ctx->ev_h1, &ctx->ev_m})
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
   // kernels that need more than 48 KB of dynamic shared memory
   const int smem_dgrad = (32 * 18 * C14_RS + 8 * 32 * 25) * 4;
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<float, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__half, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv14<__nv_bfloat16, 32, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dgrad);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__nv_bfloat16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv2_wgrad_tc<__nv_bfloat16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BYTES);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1W_TC_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_conv1_wgrad_tc<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, C1W_TC_SMEM);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_bwd_mid_tc<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, MID_SMEM_BYTES);
@@ -292,13 +302,13 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
                   ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->logits, ctx->dlogits, ctx->dflat, ctx->dy2, ctx->dp1,
                   ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
                   ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h, ctx->w2_tiles, ctx->gred,
-                  ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll, ctx->mom};
+                  ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll, ctx->mom, ctx->acc};
   for (void* p : bufs) if (p) cudaFree(p);
   if (ctx->host_mail) cudaFreeHost(const_cast<float*>(ctx->host_mail));
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
   if (ctx->side1) cudaStreamDestroy(ctx->side1);
   if (ctx->side2) cudaStreamDestroy(ctx->side2);
-  for (cudaEvent_t ev : {ctx->ev_f0, ctx->ev_j0, ctx->ev_f1, ctx->ev_j1, ctx->ev_f2, ctx->ev_j2, ctx->ev_h0, ctx->ev_h1}) if (ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : {ctx->ev_f0, ctx->ev_j0, ctx->ev_f1, ctx->ev_j1, ctx->ev_f2, ctx->ev_j2, ctx->ev_h0, ctx->ev_h1, ctx->ev_m}) if (ev) cudaEventDestroy(ev);
   delete ctx;
   return 0;
 }
@@ -551,6 +561,14 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   FcWgradArgs fw{c->p2, c->dlogits, c->gpart, B, cdiv(B, nsf)};
   if (fork) { cudaEventRecord(c->ev_f1, s); cudaStreamWaitEvent(s1, c->ev_f1, 0); }
   k_fc_wgrad<T><<<dim3(7, nsf), 224, 0, s1>>>(fw); mark();
+  const bool early_on = cfg.world > 1 && c->early_push && !c->accumulate;  // a no_sync micro-step exchanges nothing
+  if (early_on) {  // not a profile slot: it exists only at world > 1
+    PushArgs pf{c->gpart, nullptr, nsf, 0, c->comm, c->ds, 1, c->acc};
+    k_fc_reduce_push<T><<<cdiv(N_PAD - OFF_WFC, 512), 128, 0, s1>>>(pf);
+    c->last_push_fc = pf;
+    if (rec) rec->n++;
+    c->launches++;
+  }
   if (fork) cudaEventRecord(c->ev_j1, s1);
   // 7/8. BN2 backward: reduce, then d(conv2 out)
   const int ns2 = clampi(cdiv(B, 4), 1, 16);  // batch splits of the two BN2 backward kernels
@@ -565,7 +583,7 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   // small batch on the tensor-core path: BN2 backward apply, the conv2 data gradient and BN1 backward pass 1 are one
   // kernel per (image, M-tile) (bwd_mid_tc.cuh); slots 8 and 12 stay empty, slot 9 is the fused kernel
   bool mid = false;
-  if constexpr (!std::is_same<T, float>::value) mid = c->use_tc && c->fuse_mid && fuse_bn2r && B <= 32;
+  if constexpr (!std::is_same<T, float>::value) mid = c->use_tc && c->use_wgrad_tc && c->fuse_mid && fuse_bn2r && B <= 32;
   if (mid) {
     skip_slot();
   } else if (planes) {
@@ -584,9 +602,16 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   if constexpr (!std::is_same<T, float>::value) {
     if (mid) {
       tc = true;
-      BwdMidArgs ma{r2, static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dp1, c->y1, st1, c->bpart1_ll};
+      // The conv2 weight-gradient branch forks BEFORE this kernel: it rebuilds d(conv2 out) itself (k_conv2_wgrad_tc<T, true>)
+      // and only polls the BN2 backward sums this kernel's first CTA publishes, so it runs beside the backward middle
+      // instead of behind it.  d(conv2 out) is therefore never written to HBM in this mode.
+      if (fork) cudaEventRecord(c->ev_f2, s);
+      BnBwdArgs r2m = r2;
+      r2m.dy = nullptr;
+      r2m.dy_planes = nullptr;
+      BwdMidArgs ma{r2m, static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dp1, c->y1, st1, c->bpart1_ll};
       launch_k(k_bwd_mid_tc<T>, dim3(B, 2), dim3(MID_THREADS), MID_SMEM_BYTES, s, ma, pdl);
-      if (fork) cudaEventRecord(c->ev_f2, s);  // the weight-gradient branch needs this kernel's d(conv2 out) planes
+      if (fork) cudaEventRecord(c->ev_m, s);  // the side branch's row reduction also sums this kernel's conv2-bias rows
     } else if (c->use_tc) {
       tc = true;
       Conv2TcArgs t2{static_cast<char*>(c->w2_tiles) + TC_WBYTES, c->dy2h, c->params, c->dp1, nullptr, 0, st2, c->ds, c->comm, B, 0, 0, cfg.bn_eps};
@@ -606,14 +631,21 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
       // wave of SMs and shorten the row reduction behind it; DDPSTEP_WG_DIV overrides the images-per-CTA choice
       static const int wg_div = [] { const char* e = getenv("DDPSTEP_WG_DIV"); return e ? std::max(1, atoi(e)) : 2; }();  // measured at batch 32: 1 -> 45.1, 2 -> 43.0, 4 -> 44.7 us per step
       if (B <= 64) gw_rows = cdiv(B, wg_div);
-      Conv2WgradTcArgs wa{c->dy2h, c->p1h, c->gpart, B};
+      Conv2WgradTcArgs wa{c->dy2h, c->p1h, c->gpart, B, r2};
       // small batches: split the 5 kh taps over 5 CTAs per image so more SMs take part
-      k_conv2_wgrad_tc<T><<<dim3(gw_rows, B <= 64 ? 5 : 1), TC_THREADS, WG_SMEM_BYTES, s2>>>(wa);
+      if (mid) k_conv2_wgrad_tc<T, true><<<dim3(gw_rows, 5), TC_THREADS, WG_SMEM_BYTES, s2>>>(wa);
+      else k_conv2_wgrad_tc<T, false><<<dim3(gw_rows, B <= 64 ? 5 : 1), TC_THREADS, WG_SMEM_BYTES, s2>>>(wa);
     }
   }
   if (!wtc) k_conv2_wgrad<T><<<dim3(gw, 4), 160, 0, s2>>>(w2);
   mark();
-  k_reduce_rows<<<mid ? 26 : 25, 128, 0, s2>>>(c->gpart, c->gred, gw_rows, mid ? 2 * B : 0); mark();
+  if (fork && mid) cudaStreamWaitEvent(s2, c->ev_m, 0);
+  // world > 1: the side branches also push their slices of the bucket to the peers (step_kernel.cuh, "early push")
+  const int early = early_on ? 1 : 0;
+  PushArgs pr{c->gpart, c->gred, gw_rows, mid ? 2 * B : 0, c->comm, c->ds, early, c->acc};
+  k_reduce_rows<T><<<mid ? 26 : 25, 128, 0, s2>>>(pr); mark();
+  c->last_push_c2 = pr;
+  c->last_c2_ctas = mid ? 26 : 25;
   if (fork) cudaEventRecord(c->ev_j2, s2);
   // 11. BN1 backward reduce, 12. BN1 backward apply fused with conv1 weight gradient
   const int ns1 = mid ? 2 * B : clampi(B, 1, 32);  // one image per CTA at small batch: every thread has a single window, a single trip to L2
@@ -639,9 +671,8 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->host_mail, c->bnbuf, c->nbt, c->ds, c->comm, B,
               rows_c1, gw_rows, mid ? 0 : (planes ? ns2p : ns2), nsf, cfg.use_scaler, sync, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval,
-              c->mom};
-  c->last_step = sa;
-  c->last_step_dtype_ok = 1;
+              c->mom, c->post_loss ? 1 : 0, c->acc, c->accumulate ? 1 : 0, early};
+  if (!c->accumulate) { c->last_step = sa; c->last_step_dtype_ok = 1; }
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
   launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();
   return cudaGetLastError();
@@ -734,7 +765,7 @@ static int repoint(ddpstep_ctx* ctx, GraphEntry& ge, cudaGraphNode_t node, void*
 // so the 13 kernels are replayed with a single cudaGraphLaunch.
 template <bool TRAIN>
 static int run_graph(ddpstep_ctx* ctx, const BatchSrc& x, const int64_t* y, int B, cudaStream_t s) {
-  const GraphKey key(TRAIN ? 0 : 1, x.x == nullptr ? 1 : 0, y != nullptr ? 1 : 0, B);
+  const GraphKey key(TRAIN ? (ctx->accumulate ? 2 : 0) : 1, x.x == nullptr ? 1 : 0, y != nullptr ? 1 : 0, B);
   auto it = ctx->graphs.find(key);
   if (it == ctx->graphs.end()) {
     GraphEntry ge;
@@ -830,7 +861,9 @@ static int run_graph_host(ddpstep_ctx* ctx, const float* xh, const int64_t* yh, 
     cudaEventRecord(ctx->ev_h1, ctx->side1);
     cudaMemcpyAsync(ctx->x_stage, xh, xb, cudaMemcpyHostToDevice, ctx->cap_stream);
     cudaStreamWaitEvent(ctx->cap_stream, ctx->ev_h1, 0);
+    ctx->post_loss = true;
     cudaError_t e = enqueue<true>(ctx, BatchSrc{ctx->x_stage, nullptr, nullptr}, ctx->y_stage, B, ctx->cap_stream, &rec);
+    ctx->post_loss = false;
     cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &ge.graph);
     ctx->launches = before;
     if (e != cudaSuccess || e2 != cudaSuccess) {
@@ -910,6 +943,29 @@ extern "C" int ddpstep_train_step(ddpstep_ctx* ctx, const float* x, const int64_
     if (e != cudaSuccess) rc = fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
   }
   if (rc == 0) ctx->steps_enqueued++;  // only a step that was really launched will post its sequence number
+  return rc;
+}
+
+// A micro-step inside `with model.no_sync():` (torch/nn/parallel/distributed.py:1441-1470): forward, loss and
+// backward exactly as ddpstep_train_step -- BN statistics, running buffers and, under SyncBN, their exchanges included --
+// but the local gradient is ADDED to an accumulation buffer (what `.grad` does when zero_grad() is not called) and nothing
+// is exchanged, unscaled or applied.  The next ddpstep_train_step* call all-reduces buffer + its own gradient.
+extern "C" int ddpstep_train_step_accumulate(ddpstep_ctx* ctx, const float* x, const int64_t* y, int32_t batch, void* stream) {
+  int rc = check_step_args(ctx, x, batch);
+  if (rc) return rc;
+  if (!y) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const BatchSrc src{x, nullptr, nullptr};
+  ctx->accumulate = true;
+  if (ctx->cfg.use_graph) {
+    rc = run_graph<true>(ctx, src, y, batch, s);
+  } else {
+    cudaError_t e = enqueue<true>(ctx, src, y, batch, s, nullptr);
+    if (e != cudaSuccess) rc = fail(ctx, DDPSTEP_E_CUDA, "train step launch failed: %s", cudaGetErrorString(e));
+  }
+  ctx->accumulate = false;
+  if (rc == 0) ctx->steps_enqueued++;
   return rc;
 }
 
@@ -993,9 +1049,15 @@ extern "C" int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* xh, const 
     xd = ctx->x_stage;
     yd = ctx->y_stage;
   }
-  if (xd != nullptr) {
+  if (xd != nullptr) {  // pageable buffers, no graph, or zero-copy: the ordinary step, and a real synchronisation for the loss
     rc = ddpstep_train_step(ctx, xd, yd, batch, stream);
     if (rc) return rc;
+    if (loss_out) {
+      CK(cudaMemcpyAsync(loss_out, &ctx->ds->loss, sizeof(float), cudaMemcpyDeviceToHost, s));
+      CK(cudaStreamSynchronize(s));
+      return peer_failed(ctx);
+    }
+    return 0;
   }
   if (loss_out) {
     // the tail kernel posts {loss, step counter} into pinned host memory: poll it instead of copying back and
@@ -1066,6 +1128,8 @@ extern "C" int ddpstep_read_activation(ddpstep_ctx* ctx, int32_t which, void* ho
   const size_t sz[] = {B * 16 * 784 * es, B * 16 * 196 * es, B * 32 * 196 * es, B * 1568 * es, B * 10 * es,
                        B * 32 * 196 * es, B * 16 * 196 * es};
   if (which < 0 || which > 6) return fail(ctx, DDPSTEP_E_ARG, "bad activation id %d", which);
+  if (which == 5 && ctx->fuse_mid && ctx->use_tc)
+    return fail(ctx, DDPSTEP_E_STATE, "d(conv2 out) is not materialised in HBM by the fused backward middle (DDPSTEP_MID=1)");
   CK(cudaSetDevice(ctx->cfg.device));
   CK(cudaDeviceSynchronize());
   const bool planes = ctx->last_planes && (which == 1 || which == 5);
@@ -1183,6 +1247,30 @@ extern "C" int ddpstep_set_sgd(ddpstep_ctx* ctx, float lr, float momentum, float
   return 0;
 }
 
+// DDP communication-hook work for one GradBucket of any model (SURVEY 8b alternative B, 8f N3): bucket <- sum over
+// ranks of bucket * (1/W) when `average`, plain sum otherwise, in place, identical bits on every rank.  Buckets longer
+// than 29,056 elements are reduced chunk by chunk through the same double-buffered inbox the step's own gradient uses.
+// Collective and stream-ordered; must not be interleaved with an in-flight training step on another stream.
+extern "C" int ddpstep_allreduce_bucket(ddpstep_ctx* ctx, float* bucket_dev, int64_t n, int32_t average, void* stream) {
+  if (!ctx || !bucket_dev || n < 0) return fail(ctx, DDPSTEP_E_ARG, "null bucket / negative length");
+  if (reinterpret_cast<uintptr_t>(bucket_dev) & 3) return fail(ctx, DDPSTEP_E_ARG, "the bucket must be 4-byte aligned");
+  if (!ctx->peers_ready) return fail(ctx, DDPSTEP_E_STATE, "world > 1: call ddpstep_import_peers first");
+  int rc = peer_failed(ctx);
+  if (rc) return rc;
+  CK(cudaSetDevice(ctx->cfg.device));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const float pre = average ? 1.0f / (float)ctx->cfg.world : 1.0f;
+  for (int64_t off = 0; off < n; off += N_PAD) {
+    const int len = (int)std::min<int64_t>(N_PAD, n - off);
+    BucketArgs ba{bucket_dev + off, len, pre, ctx->ds, ctx->comm};
+    k_bucket_allreduce<<<cdiv(len, 1024), 256, 0, s>>>(ba);
+    k_bump_sync_epoch<<<1, 1, 0, s>>>(ctx->ds);
+    ctx->launches += 2;
+  }
+  CK(cudaGetLastError());
+  return 0;
+}
+
 // How long a kernel polls for a peer's words before it gives up (default 20 s, or DDPSTEP_PEER_TIMEOUT_MS).  NCCL in the
 // reference blocks until its watchdog fires; here a step whose wait expired applies no update and
 // every later call returns DDPSTEP_E_PEER.
@@ -1207,13 +1295,23 @@ extern "C" int ddpstep_allreduce_only(ddpstep_ctx* ctx, void* stream) {
   CK(cudaSetDevice(ctx->cfg.device));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   StepArgs sa = ctx->last_step;
+  sa.post_loss = 0;
+  const int nfc = cdiv(N_PAD - OFF_WFC, 512), nc2 = ctx->last_c2_ctas;
+  // with early push the exchange is three launches: the two side-branch kernels that finish + push 98 % of the bucket,
+  // then the tail (in a step the first two run long before the tail, here back to back)
   switch (ctx->cfg.dtype) {
-    case DDPSTEP_FP32: launch_k(k_step<float>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
-    case DDPSTEP_FP16: launch_k(k_step<__half>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
-    default: launch_k(k_step<__nv_bfloat16>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+    case DDPSTEP_FP32:
+      if (sa.early_push) { k_fc_reduce_push<float><<<nfc, 128, 0, s>>>(ctx->last_push_fc); k_reduce_rows<float><<<nc2, 128, 0, s>>>(ctx->last_push_c2); }
+      launch_k(k_step<float>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+    case DDPSTEP_FP16:
+      if (sa.early_push) { k_fc_reduce_push<__half><<<nfc, 128, 0, s>>>(ctx->last_push_fc); k_reduce_rows<__half><<<nc2, 128, 0, s>>>(ctx->last_push_c2); }
+      launch_k(k_step<__half>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+    default:
+      if (sa.early_push) { k_fc_reduce_push<__nv_bfloat16><<<nfc, 128, 0, s>>>(ctx->last_push_fc); k_reduce_rows<__nv_bfloat16><<<nc2, 128, 0, s>>>(ctx->last_push_c2); }
+      launch_k(k_step<__nv_bfloat16>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
   }
   CK(cudaGetLastError());
-  ctx->launches++;
+  ctx->launches += sa.early_push ? 3 : 1;
   ctx->steps_enqueued++;
   return 0;
 }

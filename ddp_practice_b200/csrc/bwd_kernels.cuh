@@ -172,13 +172,15 @@ __global__ void __launch_bounds__(256) k_bn_bwd_reduce(BnBwdArgs a) {
 // k2 = invstd^2 * sum_dy_xmu / N  (`batch_norm_backward_elemt`, _functions.py:170).
 // `after_wait()` runs right after the grid dependency resolved and before the sums are polled: the place for the
 // caller's loads of what the direct predecessor wrote, so that they travel together with the polls.
+// `consumer_only`: the calling grid is not the designated consumer of pass 1 (a side-branch kernel that also needs the
+// sums): none of its CTAs reduces or publishes anything, all of them poll the published words.
 template <int C, typename AfterWait>
-__device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, AfterWait&& after_wait) {
+__device__ void bn_backward_sums(const BnBwdArgs& a, float* s_k1, float* s_k2, AfterWait&& after_wait, bool consumer_only = false) {
   constexpr int OFF_G = (C == 16) ? OFF_G1 : OFF_G2, OFF_BE = (C == 16) ? OFF_BE1 : OFF_BE2;
   __shared__ float s_loc[2 * C];
   const int c = threadIdx.x;
   const bool xchg = a.sync && a.comm.world > 1;
-  const bool first = blockIdx.x == 0 && blockIdx.y == 0;
+  const bool first = !consumer_only && blockIdx.x == 0 && blockIdx.y == 0;
   // The forward statistics may have been written by the DIRECT predecessor (BN2 inside the Linear+CE kernel): they
   // are read only after the grid dependency resolved, together with the polls.
   float n_tot = 0.f, inv_c = 0.f;

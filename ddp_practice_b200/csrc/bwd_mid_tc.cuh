@@ -5,7 +5,8 @@
 // The three are chained per image -- only the BN2 sums before and the BN1 sums after need the whole batch -- so
 // fusing them removes two kernel boundaries and two trips of an activation gradient through L2: d(conv2 out) is
 // built directly in the shared-memory planes the MMA reads, d(pool1 out) goes from TMEM through registers into
-// the BN1 sums.  Both tensors are still written out (fire and forget) for the weight-gradient kernels.
+// the BN1 sums.  d(pool1 out) is still written out for the conv1 weight-gradient kernel; d(conv2 out) is not: the conv2
+// weight-gradient branch rebuilds it for itself (k_conv2_wgrad_tc<T, true>) so that it can run beside this kernel.
 //
 // grid (B, 2): CTA = one image x one 128-row M-tile of the data gradient (8 image rows), 256 threads.
 //   all threads   : zero the planes, fetch conv2-output windows (old data: before the grid dependency), then after
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(MID_THREADS, 1) k_bwd_mid_tc(BwdMidArgs a) {
       s_ws[c][phl][pw] = (o[0] + o[1]) + (o[2] + o[3]);
       const int po = (((c >> 3) * PL_PIX) + (2 * ph + 3) * 16 + 2 * pw) * 8 + (c & 7);
       stf<T>(pl + po, o[0]); stf<T>(pl + po + 8, o[1]); stf<T>(pl + po + 128, o[2]); stf<T>(pl + po + 136, o[3]);
-      if (ph >= own_lo && ph <= own_hi) {
+      if (dy != nullptr && ph >= own_lo && ph <= own_hi) {  // only when somebody downstream reads it from HBM
         const size_t off = (((size_t)n * 32 + c) * 14 + 2 * ph) * 14 + 2 * pw;
         store2<T>(dy + off, o[0], o[1]);
         store2<T>(dy + off + 14, o[2], o[3]);

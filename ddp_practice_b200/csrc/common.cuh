@@ -107,6 +107,11 @@ struct DevState {
   // Cross-rank waits give up after this many SM clock cycles (ddpstep_set_peer_timeout_ms) and raise `error`; a step
   // that saw the error applies no update (k_step) and the host API reports DDPSTEP_E_PEER.
   long long timeout_cycles;
+  // DDP.no_sync() / gradient accumulation (distributed.py:1441-1470): a micro-step adds its local (scaled, rounded)
+  // gradient to the accumulation buffer instead of exchanging it; the next ordinary step exchanges buffer + its own.
+  int acc_valid;                  // the accumulation buffer holds a gradient
+  unsigned long long sync_epoch;  // completed SYNCHRONISING steps: parity / tag of the gradient inbox (micro-steps do not
+                                  // touch the inbox, so `epoch` would let a rank run two buffers ahead of a peer)
 };
 
 // global BN statistics of the current step, written by the bn_relu_pool kernel

@@ -19,7 +19,7 @@
 //
 // ddp_main.py:23 (forward) and its autograd (ddp_main.py:91).
 #pragma once
-#include "fwd_kernels.cuh"
+#include "bwd_kernels.cuh"
 
 namespace dstep {
 
@@ -333,6 +333,11 @@ struct Conv2WgradTcArgs {
   const void* p1h;   // [B][2][320][8]
   float* gpart;      // [rows = gridDim.x][N_PAD]
   int B;
+  // BUILD = true (small batch, together with the fused backward middle, bwd_mid_tc.cuh): d(conv2 out) is not read from
+  // HBM but rebuilt here from conv2's output, the gradient at the pool output and the BN2 backward sums (the same
+  // `batch_norm_backward_elemt` arithmetic as k_bn2_bwd_apply), so this branch of the step graph depends on the
+  // Linear+CE kernel only and runs BESIDE the backward middle instead of behind it.
+  BnBwdArgs bn2;     // y = conv2 out, dpool = d(pool2 out), st = BN2 statistics, defer = 2 (sums are polled)
 };
 
 constexpr int WG_DY_STAGE = 4 * PL_BYTES, WG_P_STAGE = 2 * PL_BYTES;
@@ -346,9 +351,11 @@ template <typename T> __device__ __forceinline__ uint32_t umma_idesc_mn(int n) {
   return umma_idesc<T>(n) | (1u << 15) | (1u << 16);
 }
 
-template <typename T>
+template <typename T, bool BUILD>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcArgs a) {
   if (threadIdx.x == 0) TRACE(8 * 16 + 0);
+  __shared__ float s_k1[32], s_k2[32];
+  __shared__ float s_bn2[32][4];  // BN2 mean, invstd, gamma, beta (BUILD)
   extern __shared__ __align__(128) unsigned char wg_smem[];
   unsigned char* dy_s = wg_smem;                         // [2][4 planes]
   unsigned char* p_s = wg_smem + 2 * WG_DY_STAGE;        // [2][2 planes] + slack
@@ -359,8 +366,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
   const int kh_lo = gridDim.y == 1 ? 0 : (int)blockIdx.y, kh_n = gridDim.y == 1 ? 5 : 1;
   const uint32_t tmem_cols = gridDim.y == 1 ? 512u : 64u;
   for (int i = tid; i < 256; i += TC_THREADS) reinterpret_cast<uint32_t*>(p_s + 2 * WG_P_STAGE)[i] = 0u;
+  if (BUILD)  // the builders only ever write the 14 x 14 interior: halo rows / columns of both stages stay zero
+    for (int i = tid; i < 2 * WG_DY_STAGE / 16; i += TC_THREADS) reinterpret_cast<uint4*>(dy_s)[i] = make_uint4(0u, 0u, 0u, 0u);
   if (tid == 0) {
-    for (int s = 0; s < 2; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    // BUILD: a stage is full when the p1 planes have landed (TMA) AND the four builder warps have written d(conv2 out)
+    for (int s = 0; s < 2; ++s) { mbar_init(&full[s], BUILD ? 5 : 1); mbar_init(&empty[s], 1); }
     mbar_init(done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -378,14 +388,46 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
   const unsigned char* gdy = reinterpret_cast<const unsigned char*>(a.dy2h);
   const unsigned char* gp = reinterpret_cast<const unsigned char*>(a.p1h);
 
+  // BUILD: this thread's (up to 13) pooling windows of one image: conv2's output and the gradient at the pool output
+  constexpr int NWIN = 13;  // ceil(32 channels x 49 windows / 128 builder threads)
+  const int bt = tid - 64;  // builder thread index (warps 2..5)
+  float yw[BUILD ? NWIN : 1][4], wd[BUILD ? NWIN : 1];
+  auto fetch_windows = [&](int n) {
+    if constexpr (BUILD) {
+      const T* __restrict__ y2 = reinterpret_cast<const T*>(a.bn2.y);
+      const T* __restrict__ dfl = reinterpret_cast<const T*>(a.bn2.dpool);
+#pragma unroll
+      for (int j = 0; j < NWIN; ++j) {
+        const int wi = min(bt + j * 128, 32 * 49 - 1);
+        const int c = wi / 49, r = wi % 49, ph = r / 7, pw = r % 7;
+        const T* src = y2 + (((size_t)n * 32 + c) * 14 + 2 * ph) * 14 + 2 * pw;
+        load2<T>(src, yw[j][0], yw[j][1]);
+        load2<T>(src + 14, yw[j][2], yw[j][3]);
+        wd[j] = ldf<T>(&dfl[((size_t)n * 32 + c) * 49 + r]);
+      }
+    }
+  };
+  if constexpr (BUILD) {
+    // everything this kernel reads was written before its (full) graph dependency, the Linear+CE kernel -- except the
+    // BN2 backward sums, which CTA (0,0) of the backward-middle kernel running beside it publishes as tagged words
+    if (warp >= 2 && n_img > 0) fetch_windows(blockIdx.x);
+    bn_backward_sums<32>(a.bn2, s_k1, s_k2, [] {}, true);
+    if (tid < 32) {
+      s_bn2[tid][0] = a.bn2.st->mean[tid]; s_bn2[tid][1] = a.bn2.st->invstd[tid];
+      s_bn2[tid][2] = a.bn2.params[OFF_G2 + tid]; s_bn2[tid][3] = a.bn2.params[OFF_BE2 + tid];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) TRACE(8 * 16 + 1);
+  }
+
   if (warp == 0) {
     if (lane == 0) {
       for (int i = 0; i < n_img; ++i) {
         const int s = i & 1;
         mbar_wait(&empty[s], ((i >> 1) & 1) ^ 1);
-        mbar_expect_tx(&full[s], WG_DY_STAGE + WG_P_STAGE);
+        mbar_expect_tx(&full[s], (BUILD ? 0 : WG_DY_STAGE) + WG_P_STAGE);
         const int n = blockIdx.x + i * gridDim.x;
-        tma_bulk_g2s(dy_s + s * WG_DY_STAGE, gdy + (size_t)n * WG_DY_STAGE, WG_DY_STAGE, &full[s]);
+        if (!BUILD) tma_bulk_g2s(dy_s + s * WG_DY_STAGE, gdy + (size_t)n * WG_DY_STAGE, WG_DY_STAGE, &full[s]);
         tma_bulk_g2s(p_s + s * WG_P_STAGE, gp + (size_t)n * WG_P_STAGE, WG_P_STAGE, &full[s]);
       }
     }
@@ -418,7 +460,38 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
       }
       umma_commit(done);
     }
-  } else if ((warp & 3) < 2) {
+  }
+  if (BUILD && warp >= 2) {
+    // ===== builders: d(conv2 out) of image i straight into the MN-major B operand stage =====
+    for (int i = 0; i < n_img; ++i) {
+      const int s = i & 1;
+      if (i > 0) fetch_windows(blockIdx.x + i * gridDim.x);
+      mbar_wait(&empty[s], ((i >> 1) & 1) ^ 1);
+      T* __restrict__ pl = reinterpret_cast<T*>(dy_s + s * WG_DY_STAGE);
+#pragma unroll
+      for (int j = 0; j < NWIN; ++j) {
+        const int wi = bt + j * 128;
+        if (wi < 32 * 49) {
+          const int c = wi / 49, r = wi % 49, ph = r / 7, pw = r % 7;
+          const float mu = s_bn2[c][0], is = s_bn2[c][1], g = s_bn2[c][2], b = s_bn2[c][3];
+          bool live;
+          const int arg = pool_winner<T>(yw[j], mu, is, g, b, live);
+          const float d = live ? wd[j] : 0.f;
+          const float k1 = s_k1[c], k2 = s_k2[c], k3 = is * g;
+          const int po = (((c >> 3) * PL_PIX) + (2 * ph + 3) * 16 + 2 * pw) * 8 + (c & 7);
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            const float da = (live && q4 == arg) ? d : 0.f;
+            stf<T>(pl + po + (q4 >> 1) * 128 + (q4 & 1) * 8, rnd<T>((da - k1 - (yw[j][q4] - mu) * k2) * k3));
+          }
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to UMMA
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[s]);
+    }
+  }
+  if (warp >= 2 && (warp & 3) < 2) {
     // epilogue: accumulator row m = kw*8 + ci%8 (m < 40: TMEM lanes 0..39), column = co
     mbar_wait(done, 0);
     tc_fence_after();

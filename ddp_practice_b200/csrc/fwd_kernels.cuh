@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
 #pragma unroll
   for (int j = 0; j < 4; ++j) s[j] = ss[j] = 0.f;
 
-  for (int n = blockIdx.x; n < a.B; n += gridDim.x) {
+  for (int n = blockIdx.x; n < a.B; n += a.conv_ctas) {  // conv_ctas, not gridDim.x: the grid may carry extra filter-tile CTAs
     __syncthreads();
     for (int i = tid; i < 196; i += C1_THREADS) {  // 784 floats as 196 float4
       const float4 v = load_pixels4(a.x, n, i);

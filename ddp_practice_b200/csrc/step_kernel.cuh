@@ -43,6 +43,11 @@ struct StepArgs {
   int growth_interval;
   // lr and the other torch.optim.SGD knobs (sgd.py:425-465) are read from DevState: run-time state, see common.cuh
   float* mom;  // [N_PAD] momentum buffers
+  int post_loss;  // 1: post {loss, step counter} to host_mail (ddpstep_train_step_host polls it)
+  float* acc;     // [N_PAD] accumulation buffer of DDP.no_sync() micro-steps
+  int accumulate; // 1: micro-step inside no_sync(): add the local gradient to `acc`, exchange / apply nothing
+  int early_push; // world > 1: the conv2-filter and Linear slices were pushed by the side branches (k_reduce_rows,
+                  // k_fc_reduce_push); this kernel only gathers them
 };
 
 // conv2's filter is kept, besides its fp32 master copy, as ready-made tcgen05 B operands
@@ -56,12 +61,47 @@ struct StepArgs {
 // Sum the conv2 weight-gradient partial rows (one per wgrad CTA) in fixed row order, spread
 // over many SMs; runs on a side branch of the step graph, off the critical path, so that the
 // 8-CTA tail kernel reads one row instead of pulling rows x 51 KB through 8 SMs' L2 ports.
-__global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ gpart, float* __restrict__ gred, int rows, int rows_bias) {
+// World > 1 ("early push"): this kernel and k_fc_reduce_push below also round their slice of the gradient to the
+// autocast dtype, pre-divide it by W (reducer.hpp:276) and PUSH it into every rank's inbox -- 98 % of the bucket is on
+// the NVLink wire 10-25 us before the tail kernel starts, which then only gathers it.  The tail keeps the 544 elements
+// that exist last (conv1, the BN affine gradients, the conv2 bias).
+struct PushArgs {
+  const float* gpart;
+  float* gred;
+  int rows, rows_bias;
+  CommDev comm;
+  DevState* ds;
+  int push;  // world > 1
+  const float* acc;  // [N_PAD] no_sync accumulation buffer (added when DevState.acc_valid)
+};
+
+// one float4 of the local gradient -> tagged words in every rank's inbox (this rank's own included)
+__device__ __forceinline__ void push_grad4(const CommDev& comm, const DevState* ds, const float* acc, int e, float4 g) {
+  if (ds->acc_valid) {  // gradient accumulated by no_sync micro-steps (fp32, like `.grad`)
+    const float4 ac = *reinterpret_cast<const float4*>(acc + e);
+    g.x += ac.x; g.y += ac.y; g.z += ac.z; g.w += ac.w;
+  }
+  const unsigned long long epoch = ds->sync_epoch;
+  const int par = (int)(epoch & 1ull);
+  const unsigned int tag = (unsigned int)epoch + 1u;
+  const float inv_w = 1.0f / (float)comm.world;
+  const ulonglong2 w01 = make_ulonglong2(ll_pack(g.x * inv_w, tag), ll_pack(g.y * inv_w, tag));
+  const ulonglong2 w23 = make_ulonglong2(ll_pack(g.z * inv_w, tag), ll_pack(g.w * inv_w, tag));
+  for (int q = 0; q < comm.world; ++q) {
+    ulonglong2* dst = reinterpret_cast<ulonglong2*>(&comm.peer[q]->ll_inbox[par][comm.rank][e]);
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(w01.x), "l"(w01.y) : "memory");
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 1), "l"(w23.x), "l"(w23.y) : "memory");
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128) k_reduce_rows(PushArgs a) {
   if (threadIdx.x == 0) TRACE(14 * 16 + 0);
   const int i = (blockIdx.x * 128 + threadIdx.x) * 4;
-  if (i >= 12800 + (rows_bias > 0 ? 32 : 0)) return;
-  if (i >= 12800) rows = rows_bias;  // the conv2 bias gradient right behind the filter (bwd_mid_tc.cuh writes 2B rows)
-  const float* p = gpart + OFF_W2 + i;
+  int rows = a.rows;
+  if (i >= 12800 + (a.rows_bias > 0 ? 32 : 0)) return;
+  if (i >= 12800) rows = a.rows_bias;  // the conv2 bias gradient right behind the filter (bwd_mid_tc.cuh writes 2B rows)
+  const float* p = a.gpart + OFF_W2 + i;
   float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int r0 = 0; r0 < rows; r0 += 16) {  // sixteen predicated loads per trip to L2, row order kept
     float4 v[16];
@@ -71,8 +111,33 @@ __global__ void __launch_bounds__(128) k_reduce_rows(const float* __restrict__ g
 #pragma unroll
     for (int i = 0; i < 16; ++i) { g.x += v[i].x; g.y += v[i].y; g.z += v[i].z; g.w += v[i].w; }
   }
-  *reinterpret_cast<float4*>(gred + OFF_W2 + i) = g;
+  *reinterpret_cast<float4*>(a.gred + OFF_W2 + i) = g;
+  if (a.push && i < 12800)  // the bias tail (rows_bias) stays with the tail kernel: its region is not an early-push one
+    push_grad4(a.comm, a.ds, a.acc, OFF_W2 + i, make_float4(rnd<T>(g.x), rnd<T>(g.y), rnd<T>(g.z), rnd<T>(g.w)));
   if (threadIdx.x == 0) TRACE(14 * 16 + 15);
+}
+
+// The Linear layer's weight / bias gradient (elements OFF_WFC .. N_PARAM): sum the k_fc_wgrad partial rows in row
+// order, round, pre-divide, push.  World > 1 only; runs on the fc side branch of the step graph.
+template <typename T>
+__global__ void __launch_bounds__(128) k_fc_reduce_push(PushArgs a) {
+  if (threadIdx.x == 0) TRACE(15 * 16 + 0);
+  const int e = OFF_WFC + (blockIdx.x * 128 + threadIdx.x) * 4;
+  if (e >= N_PAD) return;
+  const float* p = a.gpart + e;
+  float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int r0 = 0; r0 < a.rows; r0 += 8) {
+    float4 v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      v[i] = r0 + i < a.rows ? __ldcg(reinterpret_cast<const float4*>(p + (size_t)(r0 + i) * N_PAD)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { g.x += v[i].x; g.y += v[i].y; g.z += v[i].z; g.w += v[i].w; }
+  }
+  g = make_float4(rnd<T>(g.x), rnd<T>(g.y), rnd<T>(g.z), rnd<T>(g.w));
+  if (e + 4 > N_PARAM) { g.z = 0.f; g.w = 0.f; }  // 29032..29035: two elements + two of padding
+  push_grad4(a.comm, a.ds, a.acc, e, g);
+  if (threadIdx.x == 0) TRACE(15 * 16 + 15);
 }
 
 template <typename T>
@@ -90,7 +155,8 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   const int e = (cta * STEP_THREADS + tid) * 4;
   const bool valid = e < N_PARAM;  // last float4 (29032..29035) is half padding
   const int W = a.comm.world, rank = a.comm.rank;
-  const unsigned long long epoch = a.ds->epoch;
+  const unsigned long long epoch = a.ds->epoch, sync_epoch = a.ds->sync_epoch;
+  const int acc_valid = a.ds->acc_valid;
   const float scale = a.ds->scale;
   const int tracker = a.ds->growth_tracker;
   const int mom_ready = a.ds->mom_ready;
@@ -140,9 +206,11 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   }
   __syncthreads();
 
+  // early push (world > 1): this thread's four elements are already in every inbox
+  const bool pushed = a.early_push && W > 1 && ((e >= OFF_W2 && e < OFF_B2) || e >= OFF_WFC);
   // ---- 1. finish the local gradient (fixed row order => deterministic)
   float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (valid) {
+  if (valid && !pushed) {
     int rows;
     bool round_t = true;
     if (e < OFF_G1) rows = a.rows_conv1;
@@ -182,14 +250,47 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   }
 
   if (threadIdx.x == 0) TRACE(13 * 16 + 2);
+  // ---- 1b. gradient accumulation (DDP.no_sync): earlier micro-steps left their sum in `acc` (fp32, as `.grad` is)
+  if (acc_valid && valid && !pushed) {
+    float4 ac = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (e + 4 <= N_PARAM) ac = *reinterpret_cast<const float4*>(a.acc + e);
+    else { ac.x = a.acc[e]; ac.y = a.acc[e + 1]; }
+    g.x += ac.x; g.y += ac.y; g.z += ac.z; g.w += ac.w;
+  }
+  if (a.accumulate) {  // a micro-step: keep the sum, exchange nothing, apply nothing (uniform branch: kernel argument)
+    if (valid) {
+      if (e + 4 <= N_PARAM) {
+        *reinterpret_cast<float4*>(a.acc + e) = g;
+        *reinterpret_cast<float4*>(a.grads_scaled + e) = g;  // tap: `.grad` after a no_sync backward
+      } else {
+        a.acc[e] = g.x; a.acc[e + 1] = g.y;
+        a.grads_scaled[e] = g.x; a.grads_scaled[e + 1] = g.y;
+      }
+    }
+    if (cta == 0 && tid < 32) {
+      const float s = warp_sum(nll_pref);
+      if (tid == 0) {
+        a.ds->loss = rnd<T>(s / (float)a.B);
+        a.ds->acc_valid = 1;
+        a.ds->epoch = epoch + 1ull;
+        if (a.host_mail != nullptr && (a.post_loss || err_before != 0)) {
+          a.host_mail[0] = rnd<T>(s / (float)a.B);
+          if (err_before != 0) reinterpret_cast<volatile int*>(a.host_mail)[2] = 1;
+          __threadfence_system();
+          reinterpret_cast<volatile unsigned int*>(a.host_mail)[1] = (unsigned int)epoch + 1u;
+        }
+      }
+    }
+    return;
+  }
   // ---- 2. DDP all-reduce: pre-divide, push to every peer's inbox, flag, wait, sum in rank order
   const float inv_w = 1.0f / (float)W;
   float4 h = make_float4(g.x * inv_w, g.y * inv_w, g.z * inv_w, g.w * inv_w);
   float4 tot = h;
   if (W > 1) {
-    const int par = (int)(epoch & 1ull);
-    const unsigned int tag = (unsigned int)epoch + 1u;
-    if (valid) {  // every element travels with its own tag: no fence, no flag, no block-level synchronisation
+    const int par = (int)(sync_epoch & 1ull);
+    const unsigned int tag = (unsigned int)sync_epoch + 1u;
+    if (valid && !pushed) {  // every element travels with its own tag: no fence, no flag, no block-level synchronisation
       const ulonglong2 w01 = make_ulonglong2(ll_pack(h.x, tag), ll_pack(h.y, tag));
       const ulonglong2 w23 = make_ulonglong2(ll_pack(h.z, tag), ll_pack(h.w, tag));
       for (int q = 0; q < W; ++q)
@@ -218,8 +319,10 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     }
     if (valid) {
       // this rank's own contribution is stored locally too, so one gather covers all W senders
-      llword* mine = &a.comm.self->ll_inbox[par][rank][e];
-      ll_store(mine, h.x, tag); ll_store(mine + 1, h.y, tag); ll_store(mine + 2, h.z, tag); ll_store(mine + 3, h.w, tag);
+      if (!pushed) {
+        llword* mine = &a.comm.self->ll_inbox[par][rank][e];
+        ll_store(mine, h.x, tag); ll_store(mine + 1, h.y, tag); ll_store(mine + 2, h.z, tag); ll_store(mine + 3, h.w, tag);
+      }
       const int idx[4] = {0, 1, 2, 3};
       tot = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
@@ -333,7 +436,11 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
       }
       if (!found && momentum != 0.f) a.ds->mom_ready = 1;
       a.ds->epoch = epoch + 1ull;
-      if (a.host_mail != nullptr) {
+      a.ds->sync_epoch = sync_epoch + 1ull;
+      a.ds->acc_valid = 0;
+      // The pinned-host mailbox costs a system-scope fence (~2 us at the very end of the step), so only the graphs of
+      // the host entry point (which polls it instead of synchronising) post to it; a voided step always raises word 2.
+      if (a.host_mail != nullptr && (a.post_loss || dead)) {
         a.host_mail[0] = rnd<T>(s / (float)a.B);
         if (dead) reinterpret_cast<volatile int*>(a.host_mail)[2] = 1;  // sticky: the host API refuses further steps
         __threadfence_system();
@@ -343,6 +450,60 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   }
   if (threadIdx.x == 0) TRACE(13 * 16 + 15);
 }
+
+// ---------------------------------------------------------------------------------------
+// The exchange on its own, for ANY fp32 bucket (alternative boundary B / 8f N3): what a DDP communication hook
+// -- `register_comm_hook(state, hook)`, hook(state, bucket) -> Future[Tensor] (distributed.py:1987-2067) -- has to do
+// for one GradBucket: bucket <- sum over ranks of bucket * (1/W)  (`_AllReduceBySumCommHook`, default_comm_hooks.hpp:36-51).
+// One launch handles one chunk of up to N_PAD elements through the same double-buffered inbox of tagged words as the
+// step's own gradient (fixed rank-order sum: identical bits on every rank); longer buckets are a sequence of launches.
+struct BucketArgs {
+  float* bucket;      // device pointer to this chunk
+  int n;              // elements in this chunk (<= N_PAD)
+  float pre_scale;    // 1/W to average like DDP's default hook, 1 for a plain SUM
+  DevState* ds;
+  CommDev comm;
+};
+
+__global__ void __launch_bounds__(256) k_bucket_allreduce(BucketArgs a) {
+  const int e = (blockIdx.x * 256 + threadIdx.x) * 4;
+  if (e >= a.n) return;
+  const int W = a.comm.world, rank = a.comm.rank;
+  const unsigned long long ep = a.ds->sync_epoch;
+  const int par = (int)(ep & 1ull);
+  const unsigned int tag = (unsigned int)ep + 1u;
+  float v[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = e + i < a.n ? a.bucket[e + i] * a.pre_scale : 0.f;
+  if (W > 1) {
+    const ulonglong2 w01 = make_ulonglong2(ll_pack(v[0], tag), ll_pack(v[1], tag));
+    const ulonglong2 w23 = make_ulonglong2(ll_pack(v[2], tag), ll_pack(v[3], tag));
+    for (int q = 0; q < W; ++q) {
+      ulonglong2* dst = reinterpret_cast<ulonglong2*>(&a.comm.peer[q]->ll_inbox[par][rank][e]);
+      asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(w01.x), "l"(w01.y) : "memory");
+      asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + 1), "l"(w23.x), "l"(w23.y) : "memory");
+    }
+    const int idx[4] = {0, 1, 2, 3};
+    float tot[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      if (half * 4 < W) {
+        float got[16];
+        ll_gather<4, 4>(&a.comm.self->ll_inbox[par][0][e], N_PAD, idx, half * 4, W, tag, got, a.ds);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)  // fixed rank order
+          if (half * 4 + q < W) { tot[0] += got[q * 4]; tot[1] += got[q * 4 + 1]; tot[2] += got[q * 4 + 2]; tot[3] += got[q * 4 + 3]; }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = tot[i];
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (e + i < a.n) a.bucket[e + i] = v[i];
+}
+// stream-ordered after a chunk: the next chunk (or the next step) uses the other inbox buffer and a fresh tag
+__global__ void k_bump_sync_epoch(DevState* ds) { ds->sync_epoch += 1ull; }
 
 // dist.reduce(size, 0, SUM); dist.reduce(correct, 0, SUM)  (ddp_main.py:108-109): every
 // rank pushes its two fp32 counters into rank 0's slots; rank 0 sums them in rank order.

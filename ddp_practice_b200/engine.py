@@ -145,6 +145,12 @@ class Engine:
         assert y.is_cuda and y.dtype == torch.int64 and y.is_contiguous()
         self._check(self.lib.ddpstep_train_step(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0], self._stream()))
 
+    def train_step_accumulate(self, x: torch.Tensor, y: torch.Tensor):
+        """A micro-step inside `with model.no_sync():` -- forward + backward, the gradient accumulated locally."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
+        assert y.is_cuda and y.dtype == torch.int64 and y.is_contiguous()
+        self._check(self.lib.ddpstep_train_step_accumulate(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0], self._stream()))
+
     def train_step_host(self, x: torch.Tensor, y: torch.Tensor, want_loss: bool = True):
         """Same from (pinned) host tensors; returns the loss (synchronises) if asked."""
         if x.is_cuda or y.is_cuda or x.dtype != torch.float32 or y.dtype != torch.int64 or not (
@@ -226,6 +232,11 @@ class Engine:
     def allreduce_only(self):
         """The tail kernel alone (all-reduce + unscale + SGD + scale update) on the last step's partial gradients."""
         self._check(self.lib.ddpstep_allreduce_only(self.ctx, self._stream()))
+
+    def allreduce_bucket(self, bucket: torch.Tensor, average: bool = True):
+        """In-place mean (or sum) over ranks of any contiguous fp32 CUDA tensor: a DDP comm hook's work for one bucket."""
+        assert bucket.is_cuda and bucket.dtype == torch.float32 and bucket.is_contiguous()
+        self._check(self.lib.ddpstep_allreduce_bucket(self.ctx, bucket.data_ptr(), bucket.numel(), int(average), self._stream()))
 
     def launch_count(self) -> int:
         return int(self.lib.ddpstep_launch_count(self.ctx))

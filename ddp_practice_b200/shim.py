@@ -13,6 +13,7 @@ module that is not the reference's ConvNet layer stack is rejected at wrap time.
 """
 from __future__ import annotations
 
+import contextlib
 import math
 import os
 import types
@@ -89,11 +90,11 @@ class _Loss:
 
 
 class _ScaledLoss:
-    def __init__(self, loss: _Loss):
-        self.loss = loss
+    def __init__(self, loss: _Loss, scaler=None):
+        self.loss, self.scaler = loss, scaler
 
     def backward(self):  # ddp_main.py:91
-        self.loss.owner._arm(self.loss, scaled=True)
+        self.loss.owner._arm(self.loss, scaled=True, scaler=self.scaler)
 
 
 class DistributedDataParallel(_tnn.Module):
@@ -130,6 +131,7 @@ class DistributedDataParallel(_tnn.Module):
         self._armed = None
         self._steps = 0
         self._mom_published = False  # optimizer.state[p]['momentum_buffer'] views handed out
+        self._no_sync = False
         self._optimizer = None       # the optimizer seen by the last step (its state holds views of our memory)
         self.last_logits = None
 
@@ -274,8 +276,32 @@ class DistributedDataParallel(_tnn.Module):
             eng = self._ensure_engine(key[0], key[1][0], None, dict(key[1][1]), batch=images.shape[0])
         return eng.eval_batch(images)  # ddp_main.py:104: real logits tensor
 
-    def _arm(self, loss: _Loss, scaled: bool):
+    def _arm(self, loss: _Loss, scaled: bool, scaler=None):
+        """`.backward()`.  Normally this only arms the step that scaler.step(optimizer) / optimizer.step() launches.
+        Inside `with model.no_sync():` (gradient accumulation, distributed.py:1441-1470) there is no optimizer step to
+        wait for: the micro-step runs now and leaves its gradient in the library's accumulation buffer."""
+        if scaler is not None:
+            scaler._owner = self
+        if self._no_sync:
+            key = self._engine_key or (scaled, (1e-4, ()))
+            eng = self._ensure_engine(scaled, key[1][0], scaler, dict(key[1][1]), batch=loss.images.shape[0])
+            labels = loss.labels.contiguous()
+            eng.train_step_accumulate(loss.images, labels if labels.dtype == torch.int64 else labels.long())
+            self._steps += 1
+            loss.step_id = self._steps
+            self.last_logits = eng.logits[: loss.images.shape[0]]
+            return
         self._armed = (loss, scaled)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """`with model.no_sync():` -- backward passes inside accumulate locally; the first one outside all-reduces
+        the accumulated gradient together with its own (same contract as torch's DDP.no_sync)."""
+        old, self._no_sync = self._no_sync, True
+        try:
+            yield
+        finally:
+            self._no_sync = old
 
     def _sync_momentum(self, optimizer, before: bool):
         """`optimizer.state[p]['momentum_buffer']` are views of the library's flat buffer.  Before a step: adopt
@@ -388,7 +414,7 @@ class GradScaler:
     def scale(self, loss):
         if not isinstance(loss, _Loss):
             raise TypeError("scaler.scale() expects the loss returned by the shim's CrossEntropyLoss on model outputs")
-        return _ScaledLoss(loss)
+        return _ScaledLoss(loss, self)
 
     def step(self, optimizer):
         params = optimizer.param_groups[0]["params"]

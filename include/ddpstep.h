@@ -122,6 +122,14 @@ int ddpstep_state_ptrs(ddpstep_ctx* ctx, ddpstep_ptrs* out);
  * graph replay.  x: [batch,1,28,28] fp32, y: [batch] int64, both DEVICE pointers.          */
 int ddpstep_train_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
                        void* stream);
+/* One iteration inside `with model.no_sync():` -- gradient accumulation, SURVEY.md 8(f) N3
+ * (torch/nn/parallel/distributed.py:1441-1470; the reference never uses it): forward, loss and
+ * backward as in ddpstep_train_step (BN statistics, running buffers and SyncBN exchanges
+ * included), but the local gradient is added to an accumulation buffer -- what `.grad` does
+ * when zero_grad() is not called -- and nothing is all-reduced, unscaled or applied.  The next
+ * ddpstep_train_step* call reduces and applies accumulated + own gradient.                   */
+int ddpstep_train_step_accumulate(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev,
+                                  int32_t batch, void* stream);
 /* Same, from HOST buffers (the `.cuda()` copies of ddp_main.py:86-87 included).  Pinned
  * buffers (cudaHostAlloc / pin_memory()) are copied by two nodes of the step graph itself,
  * pageable ones by ordinary stream-ordered copies.  If loss_out is not NULL the call returns
@@ -212,6 +220,15 @@ int ddpstep_set_peer_timeout_ms(ddpstep_ctx* ctx, double ms);
  * timed in isolation against ncclAllReduce (tools/allreduce_bench.py, bench.py `allreduce`);
  * collective: every rank calls it the same number of times.                                   */
 int ddpstep_allreduce_only(ddpstep_ctx* ctx, void* stream);
+/* The work of a DDP communication hook for one GradBucket of ANY model -- the plugin API the
+ * reference's stack already has: `DistributedDataParallel.register_comm_hook(state, hook)`,
+ * hook(state, bucket) -> Future[Tensor] (torch/nn/parallel/distributed.py:1987-2067; C++
+ * CommHookInterface::runHook, comm.hpp:104-118; SURVEY.md 8b alternative B, 8f N3).
+ * bucket <- sum over ranks of bucket * (1/W) if `average` (what DDP's default hook computes,
+ * default_comm_hooks.hpp:36-51), plain sum otherwise; in place; identical bits on every rank
+ * (fixed rank-order sum).  Any length: chunks of 29,056 elements go through the step's own
+ * double-buffered inbox.  Collective, stream-ordered.  ddp_practice_b200/comm_hook.py wraps it. */
+int ddpstep_allreduce_bucket(ddpstep_ctx* ctx, float* bucket_dev, int64_t n, int32_t average, void* stream);
 /* Number of kernel launches (graph kernel nodes count one each) issued so far.             */
 int64_t ddpstep_launch_count(const ddpstep_ctx* ctx);
 /* Device-side error word (peer timeout), 0 = healthy.  Synchronises the device.  The step

@@ -108,6 +108,48 @@ def main():
         other = mine.clone()
         dist.broadcast(other, 0)
         assert torch.equal(mine, other), f"rank {rank} diverged from rank 0 at step {s}"
+    # ---- DDP.no_sync() / gradient accumulation (distributed.py:1441-1470): one micro-step whose gradient
+    # stays local, then a synchronising step that all-reduces the sum -- twice
+    xa, ya = O.synthetic_mnist(4 * B * world, seed=21)
+    xa, ya = xa[rank::world].cuda(), ya[rank::world].cuda()
+    acc_steps = []
+    for s in range(2):
+        x1, y1 = xa[(2 * s) * B:(2 * s + 1) * B].contiguous(), ya[(2 * s) * B:(2 * s + 1) * B].contiguous()
+        x2, y2 = xa[(2 * s + 1) * B:(2 * s + 2) * B].contiguous(), ya[(2 * s + 1) * B:(2 * s + 2) * B].contiguous()
+        model.train()
+        tr.optimizer.zero_grad()
+        with model.no_sync():
+            l1 = tr.criterion(model(x1), y1)
+            (tr.scaler.scale(l1) if amp else l1).backward()
+        l2 = tr.criterion(model(x2), y2)
+        (tr.scaler.scale(l2) if amp else l2).backward()
+        if amp:
+            tr.scaler.unscale_(tr.optimizer)
+        from tests.refmodel import flat_grads
+        g_ref = flat_grads(model)
+        finite = bool(torch.isfinite(g_ref).all())
+        if amp:
+            tr.scaler.step(tr.optimizer)
+            tr.scaler.update()
+        else:
+            tr.optimizer.step()
+        eng.train_step_accumulate(x1, y1)
+        eng.train_step(x2, y2)
+        torch.cuda.synchronize()
+        eng.check_device()
+        assert eng.found_inf.item() == (0.0 if finite else 1.0), (rank, "no_sync", s)
+        if amp:
+            assert eng.scale.item() == tr.scaler.get_scale() and eng.growth_tracker.item() == int(tr.scaler._growth_tracker.item())
+        assert abs(eng.loss.item() - float(l2.item())) <= tol * abs(float(l2.item()))
+        if finite:
+            errs = grad_errors(eng.grads.cpu(), g_ref)
+            acc_steps.append(max(errs.values()))
+            assert_grads_close(eng.grads.cpu(), g_ref, flip_tol, f"rank {rank} no_sync step {s}")  # flips not counted here
+        mine = torch.cat([eng.params, eng.grads, eng.bn_buffers]).clone().view(torch.int32)
+        other = mine.clone()
+        dist.broadcast(other, 0)
+        assert torch.equal(mine, other), f"rank {rank} diverged from rank 0 in no_sync step {s}"
+
     got = eng.read_state()
     assert torch.allclose(torch.from_numpy(got["params"]), flat_params(model), rtol=1e-4, atol=2e-6)
     # the reference's buffers are compared after its next forward-time broadcast (plain BN) / directly (SyncBN)
@@ -165,7 +207,7 @@ def main():
         print(json.dumps({"ok": True, "dtype": dtype, "world": world, "sync_bn": sync_bn, "batch": B,
                           "worst_grad_rel_l2": max([r["worst_rel_l2"] or 0.0 for r in per_step]),
                           "steps_needing_flip_tol": sum(1 for r in per_step if r["flips"] > 0 and r["tol"] is not None),
-                          "per_step": per_step, "correct": c, "size": sz, "ref_correct": correct.item(),
+                          "per_step": per_step, "no_sync_worst_rel_l2": acc_steps, "correct": c, "size": sz, "ref_correct": correct.item(),
                           "near_tie_prediction_flips": tie_flips.item(), "non_tie_prediction_flips": hard_flips.item(),
                           "min_top2_rel_margin": min_margin.item()}), flush=True)
     eng.close()

@@ -95,3 +95,47 @@ def test_oracle_matches_live_two_process_gloo_ddp():
     shards = [[(xt[r::world][lo:lo + 16], yt[r::world][lo:lo + 16]) for lo in range(0, 40, 16)] for r in range(world)]
     c, s = O.test_counts(st, shards, "fp32")
     assert (c, s) == (r0["correct"], r0["size"]) and s == 80.0
+
+
+def _hook_worker(rank, world, port, ret):
+    """The comm-hook contract (distributed.py:1987-2067) with the hook's reducer swapped for gloo: what must hold for
+    ddp_practice_b200.comm_hook on any model -- >= 2 buckets, one Future per bucket, mean over ranks, replicas equal."""
+    from ddp_practice_b200.comm_hook import B200AllreduceState, b200_allreduce_hook
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+
+    def make():
+        torch.manual_seed(7)
+        return nn.Sequential(nn.Linear(64, 600), nn.ReLU(), nn.Linear(600, 600), nn.ReLU(), nn.Linear(600, 10))
+
+    def gloo_mean(t):
+        dist.all_reduce(t)
+        t.div_(world)
+
+    plain = nn.parallel.DistributedDataParallel(make(), bucket_cap_mb=0.2)
+    hooked = nn.parallel.DistributedDataParallel(make(), bucket_cap_mb=0.2)
+    state = B200AllreduceState(gloo_mean)
+    hooked.register_comm_hook(state, b200_allreduce_hook)
+    torch.manual_seed(100 + rank)
+    x, y = torch.randn(16, 64), torch.randint(0, 10, (16,))
+    # iteration 0 always runs with ONE bucket (distributed.py:1224-1225); the Reducer rebuilds its buckets under
+    # bucket_cap_mb after it (reducer.hpp:299-301), so the second iteration is the one with several
+    for it in range(2):
+        for m in (plain, hooked):
+            m.zero_grad()
+            nn.functional.cross_entropy(m(x), y).backward()
+    same = all(torch.allclose(a.grad, b.grad, rtol=1e-6, atol=1e-8) for a, b in zip(plain.parameters(), hooked.parameters()))
+    ret[rank] = {"same": same, "buckets": state.buckets_seen,
+                 "grad0": torch.cat([p.grad.reshape(-1) for p in hooked.parameters()])}
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_comm_hook_contract_two_process_gloo():
+    world, port = 2, 29671
+    ret = mp.Manager().dict()
+    mp.spawn(_hook_worker, args=(world, port, ret), nprocs=world, join=True)
+    assert ret[0]["same"] and ret[1]["same"]
+    assert ret[0]["buckets"] >= 3 and ret[0]["buckets"] == ret[1]["buckets"]  # 1 (iteration 0) + >= 2 (bucket_cap_mb)
+    assert torch.equal(ret[0]["grad0"], ret[1]["grad0"])

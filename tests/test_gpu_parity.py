@@ -372,6 +372,57 @@ def test_sgd_momentum_weight_decay_nesterov_match_torch_on_the_same_gradients(dt
     e.close()
 
 
+@pytest.mark.parametrize("dtype", ["fp16", "bf16", "fp32"])
+def test_gradient_accumulation_matches_torch(dtype):
+    """SURVEY 8(f) N3, `no_sync` / gradient accumulation: a micro-step (ddpstep_train_step_accumulate) leaves its gradient
+    in the accumulation buffer, the next ordinary step reduces and applies the sum.  Against torch eager doing the same
+    with two backward passes per optimizer step (at world 1 DDP.no_sync() is exactly that)."""
+    torch.manual_seed(3407)
+    amp = dtype != "fp32"
+    model = RefConvNet(TDT[dtype], "cuda").cuda()
+    tr = RefTrainer(model, amp)
+    e = _engine(dtype=dtype, batch_cap=32, use_scaler=amp)
+    e.load_state(flat_params(model).numpy(), bn_buffers(model).numpy())
+    x, y = O.synthetic_mnist(32 * 2 * 4 + 12)
+    x, y = x.cuda(), y.cuda()
+    from tests.refmodel import flat_grads
+    tol = AMP_FLIP_TOL if amp else 1e-3  # routing flips are not counted in this test
+    for s in range(4):
+        lo = 64 * s
+        x1, y1, x2, y2 = x[lo:lo + 32].contiguous(), y[lo:lo + 32].contiguous(), x[lo + 32:lo + 64].contiguous(), y[lo + 32:lo + 64].contiguous()
+        if s == 3:  # a ragged micro-batch
+            x1, y1 = x[256:268].contiguous(), y[256:268].contiguous()
+        model.train()
+        tr.optimizer.zero_grad()
+        l1 = tr.criterion(model(x1), y1)
+        (tr.scaler.scale(l1) if amp else l1).backward()
+        l2 = tr.criterion(model(x2), y2)
+        (tr.scaler.scale(l2) if amp else l2).backward()
+        if amp:
+            tr.scaler.unscale_(tr.optimizer)
+        g_ref = flat_grads(model)
+        finite = bool(torch.isfinite(g_ref).all())
+        if amp:
+            tr.scaler.step(tr.optimizer)
+            tr.scaler.update()
+        else:
+            tr.optimizer.step()
+        e.train_step_accumulate(x1, y1)
+        torch.cuda.synchronize()
+        assert e.loss.item() == pytest.approx(float(l1.item()), rel=AMP_TOL if amp else 1e-4, nan_ok=True)
+        e.train_step(x2, y2)
+        torch.cuda.synchronize()
+        assert e.found_inf.item() == (0.0 if finite else 1.0), f"step {s}"
+        if amp:
+            assert (e.scale.item(), e.growth_tracker.item()) == (tr.scaler.get_scale(), int(tr.scaler._growth_tracker.item()))
+        if finite:
+            assert_grads_close(e.grads.cpu(), g_ref, tol, f"{dtype} accumulated step {s}")
+    got = e.read_state()
+    assert np.allclose(got["params"], flat_params(model).numpy(), rtol=1e-4 if amp else 1e-5, atol=2e-6 if amp else 1e-7)
+    assert list(got["nbt"]) == nbt(model) == [8, 8]
+    e.close()
+
+
 def test_lr_schedule_changes_run_time_state_not_the_context():
     """an LR scheduler must not rebuild anything.  `ddpstep_set_sgd` changes lr (and the other knobs) between
     steps; parameters keep matching torch.optim.SGD bit for bit, the GradScaler state keeps its own trajectory, and the

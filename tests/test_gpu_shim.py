@@ -181,3 +181,46 @@ def test_momentum_sgd_through_the_shim_and_optimizer_checkpoint_resume(tmp_path)
     torch.cuda.synchronize()
     assert torch.equal(flat_params(m2), flat_params(m0))
     assert torch.equal(m2.engine.momentum_buffer, m0.engine.momentum_buffer)
+
+
+def test_shim_lr_scheduler_and_no_sync_keep_one_context():
+    """an LR scheduler stepping `param_groups[0]['lr']` must not rebuild the native context nor
+    reset the live GradScaler state; `with model.no_sync():` accumulates like torch's DDP.  Loop written the way a user
+    of the reference would extend it; compared bit for bit with the C ABI driven directly."""
+    from ddp_practice_b200 import Engine
+    from ddp_practice_b200.shim import GradScaler, nn
+    torch.manual_seed(3407)
+    model = RefConvNet(torch.float16, "cuda").cuda()
+    init_p, init_bn = flat_params(model).numpy(), bn_buffers(model).numpy()
+    model = nn.parallel.DistributedDataParallel(nn.SyncBatchNorm.convert_sync_batchnorm(model), device_ids=[0])
+    criterion = nn.CrossEntropyLoss().cuda()
+    optimizer = torch.optim.SGD(model.parameters(), 1e-2, momentum=0.9)
+    sched = torch.optim.lr_scheduler.StepLR(optimizer, step_size=1, gamma=0.5)
+    scaler = GradScaler(growth_interval=3)
+    x, y = O.synthetic_mnist(32 * 8)
+    x, y = x.cuda(), y.cuda()
+    e = Engine(dtype="fp16", batch_cap=32, lr=1e-2, momentum=0.9, growth_interval=3)
+    e.load_state(init_p, init_bn)
+    model.train()
+    engines = set()
+    for s in range(4):
+        xa, ya, xb, yb = x[64 * s:64 * s + 32], y[64 * s:64 * s + 32], x[64 * s + 32:64 * s + 64], y[64 * s + 32:64 * s + 64]
+        optimizer.zero_grad()
+        with model.no_sync():  # micro-step: the gradient stays in the accumulation buffer
+            scaler.scale(criterion(model(xa), ya)).backward()
+        loss = criterion(model(xb), yb)
+        scaler.scale(loss).backward()
+        scaler.step(optimizer)
+        scaler.update()
+        sched.step()
+        engines.add(id(model.engine))
+        e.train_step_accumulate(xa.contiguous(), ya.contiguous())
+        e.train_step(xb.contiguous(), yb.contiguous())
+        e.set_sgd(optimizer.param_groups[0]["lr"], momentum=0.9)
+        torch.cuda.synchronize()
+        assert loss.item() == e.loss.item()
+        assert scaler.get_scale() == e.scale.item() and scaler.state_dict()["_growth_tracker"] == e.growth_tracker.item()
+        assert torch.equal(flat_params(model), e.params.cpu()), f"step {s}"
+    assert len(engines) == 1, "the native context was rebuilt"
+    assert optimizer.param_groups[0]["lr"] == pytest.approx(1e-2 * 0.5 ** 4)
+    e.close()

@@ -87,27 +87,39 @@ def main():
         eng.train_step(x[s * 32:(s + 1) * 32].contiguous(), y[s * 32:(s + 1) * 32].contiguous())
     torch.cuda.synchronize()
     r = timed(eng.allreduce_only)
-    res["ours"] = dict(r, **bw(r["p50_us"]), what="k_step alone: all-reduce + unscale + non-finite check + SGD + scale update")
+    res["ours_fused_tail_eager"] = dict(r, **bw(r["p50_us"]), what="ddpstep_allreduce_only, eager launches from Python (host-bound): "
+                                        "all-reduce + unscale + non-finite check + SGD + scale update")
+    eng.check_device()
+
+    def graphed(fn, what, key):
+        """50 calls per CUDA-graph replay: no host launch overhead, the device-side cost of one call"""
+        try:
+            g = torch.cuda.CUDAGraph()
+            sg = torch.cuda.Stream()
+            with torch.cuda.stream(sg):
+                for _ in range(3):
+                    fn()
+                torch.cuda.synchronize()
+                with torch.cuda.graph(g, stream=sg):
+                    for _ in range(50):
+                        fn()
+            r = timed(g.replay, iters=max(args.iters // 50, 10), per_call=50)
+            res[key] = dict(r, **bw(r["p50_us"]), what=what + "; 50 calls per CUDA-graph replay")
+        except Exception as e:  # noqa: BLE001
+            res[key] = {"unavailable": repr(e)[:200]}
+
+    graphed(eng.allreduce_only, "the fused tail (all-reduce + unscale + inf check + SGD + scale update)", "ours_fused_tail")
+    eng.check_device()
+    plain = torch.randn(29034, device="cuda")
+    graphed(lambda: eng.allreduce_bucket(plain), "ddpstep_allreduce_bucket: the bare exchange of the same 116,136 bytes "
+            "(the comm-hook entry point)", "ours_bare_exchange")
     eng.check_device()
 
     # ---- NCCL, as the reference calls it
     bucket = torch.randn(29034, device="cuda")
     r = timed(lambda: dist.all_reduce(bucket))
     res["nccl"] = dict(r, **bw(r["p50_us"]), what="dist.all_reduce, eager launches")
-    try:
-        g = torch.cuda.CUDAGraph()
-        sg = torch.cuda.Stream()
-        with torch.cuda.stream(sg):
-            for _ in range(3):
-                dist.all_reduce(bucket)
-            torch.cuda.synchronize()
-            with torch.cuda.graph(g, stream=sg):
-                for _ in range(50):
-                    dist.all_reduce(bucket)
-        r = timed(g.replay, iters=max(args.iters // 50, 10), per_call=50)
-        res["nccl_graph"] = dict(r, **bw(r["p50_us"]), what="50 all_reduce calls per CUDA-graph replay")
-    except Exception as e:  # noqa: BLE001
-        res["nccl_graph"] = {"unavailable": repr(e)[:200]}
+    graphed(lambda: dist.all_reduce(bucket), "dist.all_reduce (NCCL)", "nccl_graph")
 
     # ---- torch symmetric memory one-shot kernels
     try:
@@ -118,9 +130,11 @@ def main():
         name = dist.group.WORLD.group_name
         r = timed(lambda: torch.ops.symm_mem.one_shot_all_reduce(t, "sum", name))
         res["symm_one_shot"] = dict(r, **bw(r["p50_us"]), what="torch.ops.symm_mem.one_shot_all_reduce")
+        graphed(lambda: torch.ops.symm_mem.one_shot_all_reduce(t, "sum", name), "torch.ops.symm_mem.one_shot_all_reduce", "symm_one_shot_graph")
         try:
             r = timed(lambda: torch.ops.symm_mem.multimem_one_shot_all_reduce(t, "sum", name))
             res["symm_multimem"] = dict(r, **bw(r["p50_us"]), what="torch.ops.symm_mem.multimem_one_shot_all_reduce (NVLS)")
+            graphed(lambda: torch.ops.symm_mem.multimem_one_shot_all_reduce(t, "sum", name), "multimem_one_shot_all_reduce (NVLS)", "symm_multimem_graph")
         except Exception as e:  # noqa: BLE001
             res["symm_multimem"] = {"unavailable": repr(e)[:200]}
     except Exception as e:  # noqa: BLE001
@@ -135,7 +149,7 @@ def main():
     r = timed(lambda: dist.all_reduce(small))
     res["nccl_allreduce_256B"] = r
 
-    eng.close()
+    # (no eng.close(): the process leaves through os._exit below)
     if rank == 0:
         line = json.dumps(res)
         print(line, flush=True)
@@ -143,8 +157,10 @@ def main():
             os.makedirs(os.path.dirname(os.path.abspath(args.out)), exist_ok=True)
             with open(args.out, "w") as f:
                 f.write(line + "\n")
-    dist.barrier()
-    dist.destroy_process_group()
+    # CUDA graphs holding NCCL / symmetric-memory work make an orderly teardown hang on this stack: results are out, leave
+    sys.stdout.flush()
+    torch.cuda.synchronize()
+    os._exit(0)
 
 
 if __name__ == "__main__":
