@@ -336,9 +336,10 @@ def main():
     # the long form (adds symmetric-memory one-shot and the SyncBN-sized exchanges).
     allreduce = None
     if world > 1:
-        n_ar = 200
-        def timed(fn):
-            for _ in range(20):
+        n_ar, per = 40, 25
+
+        def timed(fn, per_call):
+            for _ in range(5):
                 fn()
             barrier()
             a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -349,16 +350,38 @@ def main():
                 fn()
             a1.record()
             barrier()
-            return max_over_ranks(a0.elapsed_time(a1)) / n_ar * 1e3
+            return max_over_ranks(a0.elapsed_time(a1)) / n_ar / per_call * 1e3
+
+        def graph_of(fn):  # `per` calls of OUR kernels in one CUDA graph: device-side cost, no host launch overhead
+            g, sg = torch.cuda.CUDAGraph(), torch.cuda.Stream()
+            with torch.cuda.stream(sg):
+                fn()
+                torch.cuda.synchronize()
+                with torch.cuda.graph(g, stream=sg):
+                    for _ in range(per):
+                        fn()
+            return g
+
         bucket = torch.zeros(29034, device="cuda")
-        ours_us = timed(eng.allreduce_only)
-        nccl_us = timed(lambda: dist.all_reduce(bucket))
+        mine = torch.zeros(29034, device="cuda")
+        barrier()
+        g_bare, g_tail = graph_of(lambda: eng.allreduce_bucket(mine)), graph_of(eng.allreduce_only)
+        bare_us = timed(g_bare.replay, per)
+        tail_us = timed(g_tail.replay, per)
+        nccl_us = timed(lambda: dist.all_reduce(bucket), 1)
+        del g_bare, g_tail
         S = 116136
-        allreduce = {"bytes": S, "latency_us": ours_us, "nccl_latency_us": nccl_us,
-                     "algbw_gbs": S / (ours_us * 1e-6) / 1e9, "busbw_gbs": S / (ours_us * 1e-6) / 1e9 * 2 * (world - 1) / world,
-                     "nccl_busbw_gbs": S / (nccl_us * 1e-6) / 1e9 * 2 * (world - 1) / world, "nvlink_peak_gbs_per_dir": 900.0,
-                     "what": f"mean of {n_ar} back-to-back launches; ours = ddpstep_allreduce_only (k_step: all-reduce + unscale + "
-                             "non-finite check + SGD + scale update fused), NCCL = dist.all_reduce of the bare bucket"}
+        bus = lambda us: S / (us * 1e-6) / 1e9 * 2 * (world - 1) / world
+        allreduce = {"bytes": S, "latency_us": bare_us, "busbw_gbs": bus(bare_us), "algbw_gbs": S / (bare_us * 1e-6) / 1e9,
+                     "fused_tail_us": tail_us, "nccl_latency_us": nccl_us, "nccl_busbw_gbs": bus(nccl_us),
+                     "nvlink_peak_gbs_per_dir": 900.0,
+                     "what": f"latency_us: ddpstep_allreduce_bucket on the 116,136-byte bucket (the bare one-shot exchange), {per} calls per "
+                             f"CUDA-graph replay x {n_ar} replays; fused_tail_us: ddpstep_allreduce_only (exchange + unscale + non-finite "
+                             "check + SGD + scale update, what the step runs); nccl_latency_us: dist.all_reduce of the same bucket "
+                             "issued eagerly, as the reference's Reducer issues it (reducer.hpp:524).  Device-timed, max over ranks.  "
+                             "The message is latency-bound: 116 KB is 0.13 us of NVLink wire time.  tools/allreduce_bench.py adds NCCL "
+                             "inside a CUDA graph, torch's symmetric-memory one-shot and the NVLS multimem kernel "
+                             "(profiles/r02_allreduce_w*.json)"}
         eng.check_device()
 
     # ---- per-kernel device times (graph with event nodes), for the roofline of the dominant kernel

@@ -633,7 +633,10 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
       if (B <= 64) gw_rows = cdiv(B, wg_div);
       Conv2WgradTcArgs wa{c->dy2h, c->p1h, c->gpart, B, r2};
       // small batches: split the 5 kh taps over 5 CTAs per image so more SMs take part
-      if (mid) k_conv2_wgrad_tc<T, true><<<dim3(gw_rows, 5), TC_THREADS, WG_SMEM_BYTES, s2>>>(wa);
+      if (mid) {
+        gw_rows = B;  // one image per CTA: rebuilding d(conv2 out) is the long part of this kernel, so it is not serialised
+        k_conv2_wgrad_tc<T, true><<<dim3(gw_rows, 5), WG_BUILD_THREADS, WG_SMEM_BYTES, s2>>>(wa);
+      }
       else k_conv2_wgrad_tc<T, false><<<dim3(gw_rows, B <= 64 ? 5 : 1), TC_THREADS, WG_SMEM_BYTES, s2>>>(wa);
     }
   }

@@ -351,8 +351,12 @@ template <typename T> __device__ __forceinline__ uint32_t umma_idesc_mn(int n) {
   return umma_idesc<T>(n) | (1u << 15) | (1u << 16);
 }
 
+constexpr int WG_BUILD_THREADS = 64 + 320;  // BUILD: warp 0 TMA, warp 1 MMA, warps 2..11 builders (warps 4, 5 also the epilogue)
+
 template <typename T, bool BUILD>
-__global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcArgs a) {
+__global__ void __launch_bounds__(BUILD ? WG_BUILD_THREADS : TC_THREADS, BUILD ? 2 : 1) k_conv2_wgrad_tc(Conv2WgradTcArgs a) {
+  constexpr int NTHREADS = BUILD ? WG_BUILD_THREADS : TC_THREADS;
+  constexpr int NBUILD = NTHREADS - 64;
   if (threadIdx.x == 0) TRACE(8 * 16 + 0);
   __shared__ float s_k1[32], s_k2[32];
   __shared__ float s_bn2[32][4];  // BN2 mean, invstd, gamma, beta (BUILD)
@@ -365,12 +369,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kh_lo = gridDim.y == 1 ? 0 : (int)blockIdx.y, kh_n = gridDim.y == 1 ? 5 : 1;
   const uint32_t tmem_cols = gridDim.y == 1 ? 512u : 64u;
-  for (int i = tid; i < 256; i += TC_THREADS) reinterpret_cast<uint32_t*>(p_s + 2 * WG_P_STAGE)[i] = 0u;
+  for (int i = tid; i < 256; i += NTHREADS) reinterpret_cast<uint32_t*>(p_s + 2 * WG_P_STAGE)[i] = 0u;
   if (BUILD)  // the builders only ever write the 14 x 14 interior: halo rows / columns of both stages stay zero
-    for (int i = tid; i < 2 * WG_DY_STAGE / 16; i += TC_THREADS) reinterpret_cast<uint4*>(dy_s)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < 2 * WG_DY_STAGE / 16; i += NTHREADS) reinterpret_cast<uint4*>(dy_s)[i] = make_uint4(0u, 0u, 0u, 0u);
   if (tid == 0) {
     // BUILD: a stage is full when the p1 planes have landed (TMA) AND the four builder warps have written d(conv2 out)
-    for (int s = 0; s < 2; ++s) { mbar_init(&full[s], BUILD ? 5 : 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&full[s], BUILD ? 1 + NBUILD / 32 : 1); mbar_init(&empty[s], 1); }
     mbar_init(done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -389,8 +393,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
   const unsigned char* gp = reinterpret_cast<const unsigned char*>(a.p1h);
 
   // BUILD: this thread's (up to 13) pooling windows of one image: conv2's output and the gradient at the pool output
-  constexpr int NWIN = 13;  // ceil(32 channels x 49 windows / 128 builder threads)
-  const int bt = tid - 64;  // builder thread index (warps 2..5)
+  constexpr int NWIN = (32 * 49 + NBUILD - 1) / NBUILD;  // windows per builder thread (5 with 320 builders)
+  const int bt = tid - 64;  // builder thread index (warps 2 and up)
   float yw[BUILD ? NWIN : 1][4], wd[BUILD ? NWIN : 1];
   auto fetch_windows = [&](int n) {
     if constexpr (BUILD) {
@@ -398,7 +402,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
       const T* __restrict__ dfl = reinterpret_cast<const T*>(a.bn2.dpool);
 #pragma unroll
       for (int j = 0; j < NWIN; ++j) {
-        const int wi = min(bt + j * 128, 32 * 49 - 1);
+        const int wi = min(bt + j * NBUILD, 32 * 49 - 1);
         const int c = wi / 49, r = wi % 49, ph = r / 7, pw = r % 7;
         const T* src = y2 + (((size_t)n * 32 + c) * 14 + 2 * ph) * 14 + 2 * pw;
         load2<T>(src, yw[j][0], yw[j][1]);
@@ -470,7 +474,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
       T* __restrict__ pl = reinterpret_cast<T*>(dy_s + s * WG_DY_STAGE);
 #pragma unroll
       for (int j = 0; j < NWIN; ++j) {
-        const int wi = bt + j * 128;
+        const int wi = bt + j * NBUILD;
         if (wi < 32 * 49) {
           const int c = wi / 49, r = wi % 49, ph = r / 7, pw = r % 7;
           const float mu = s_bn2[c][0], is = s_bn2[c][1], g = s_bn2[c][2], b = s_bn2[c][3];
@@ -491,7 +495,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_conv2_wgrad_tc(Conv2WgradTcAr
       if (lane == 0) mbar_arrive(&full[s]);
     }
   }
-  if (warp >= 2 && (warp & 3) < 2) {
+  if (warp == 4 || warp == 5) {  // TMEM lane quarters 0 and 1
     // epilogue: accumulator row m = kw*8 + ci%8 (m < 40: TMEM lanes 0..39), column = co
     mbar_wait(done, 0);
     tc_fence_after();
