@@ -395,7 +395,7 @@ def main():
     es = 4 if args.dtype == "fp32" else 2
     roof = roofline_of(prof, B, es, hbm_peak, tf_peak, peak_src, n_prof)
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r02_traffic.json")
     if os.path.exists(tpath) and B == 32 and args.dtype == "fp16":  # the capture was taken on this configuration
         traffic = json.load(open(tpath)).get(roof["kernel"])
     roof["traffic"] = traffic
