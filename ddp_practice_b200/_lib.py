@@ -43,6 +43,8 @@ SYMBOLS = [
     ("ddpstep_set_scaler", C.c_int, [_P, C.c_float, C.c_int32]),
     ("ddpstep_state_ptrs", C.c_int, [_P, C.POINTER(Ptrs)]),
     ("ddpstep_train_step", C.c_int, [_P, _P, _P, C.c_int32, _P]),
+    ("ddpstep_train_steps", C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, _P]),
+    ("ddpstep_train_steps_indexed", C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, _P]),
     ("ddpstep_train_step_accumulate", C.c_int, [_P, _P, _P, C.c_int32, _P]),
     ("ddpstep_train_step_host", C.c_int, [_P, _P, _P, C.c_int32, _P, _P]),
     ("ddpstep_train_step_indexed", C.c_int, [_P, _P, _P, _P, C.c_int32, _P]),

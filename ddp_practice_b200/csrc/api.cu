@@ -86,6 +86,8 @@ struct ddpstep_ctx {
   std::vector<void*> opened;
   // one captured graph per (mode, where the batch comes from, labels present, batch size)
   std::map<GraphKey, GraphEntry> graphs;
+  // (source kind, n_steps, batch, dataset pointer, label pointer) -> K training steps captured as ONE graph
+  std::map<std::tuple<int, int, int, const void*, const void*>, GraphEntry> multi_graphs;
   cudaStream_t cap_stream = nullptr, side1 = nullptr, side2 = nullptr;
   cudaEvent_t ev_f0 = nullptr, ev_j0 = nullptr, ev_f1 = nullptr, ev_j1 = nullptr, ev_f2 = nullptr, ev_j2 = nullptr;
   cudaEvent_t ev_h0 = nullptr, ev_h1 = nullptr, ev_m = nullptr;
@@ -96,6 +98,9 @@ struct ddpstep_ctx {
   volatile float* host_mail = nullptr;  // pinned, mapped: {loss, completed-step counter}
   unsigned int steps_enqueued = 0;     // training steps launched so far (matches DevState.epoch once they finish)
   bool early_push = true;              // world > 1: side branches push their gradient slices (DDPSTEP_EARLY_PUSH=0: the tail does)
+  bool chained_step = false;           // the step being enqueued follows another one inside the same captured graph
+  float* xs_stage = nullptr; int64_t* ys_stage = nullptr; long long* idx_stage = nullptr;  // multi-step staging (lazy)
+  size_t multi_cap = 0;                // images the multi-step staging buffers hold
   bool post_loss = false;              // the step being enqueued posts its loss to the pinned mailbox (host entry point)
   int sm_khz = 1965000;                // SM clock used to turn the peer timeout into clock64() cycles
   StepArgs last_step;                  // arguments of the most recently enqueued tail kernel (ddpstep_allreduce_only)
@@ -290,6 +295,11 @@ static void drop_graphs(ddpstep_ctx* ctx) {
     if (kv.second.graph) cudaGraphDestroy(kv.second.graph);
   }
   ctx->graphs.clear();
+  for (auto& kv : ctx->multi_graphs) {
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    if (kv.second.graph) cudaGraphDestroy(kv.second.graph);
+  }
+  ctx->multi_graphs.clear();
 }
 
 extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
@@ -302,7 +312,8 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
                   ctx->y1, ctx->p1, ctx->y2, ctx->p2, ctx->logits, ctx->dlogits, ctx->dflat, ctx->dy2, ctx->dp1,
                   ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
                   ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h, ctx->w2_tiles, ctx->gred,
-                  ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll, ctx->mom, ctx->acc};
+                  ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll, ctx->mom, ctx->acc,
+                  ctx->xs_stage, ctx->ys_stage, ctx->idx_stage};
   for (void* p : bufs) if (p) cudaFree(p);
   if (ctx->host_mail) cudaFreeHost(const_cast<float*>(ctx->host_mail));
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
@@ -509,7 +520,8 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
       k_conv1_tc<T><<<rows1, C1T_THREADS, C1T_SMEM, s>>>(t1);
     }
   }
-  if (!c1tc) k_conv1_fwd<T><<<dim3(g1 + (tiles_in_conv1 ? kTileCtas : 0), C1_GROUPS), C1_THREADS, 0, s>>>(a1);
+  // in a multi-step graph the conv1 of step s > 0 hangs off the previous step's tail kernel by a programmatic edge
+  if (!c1tc) launch_k(k_conv1_fwd<T>, dim3(g1 + (tiles_in_conv1 ? kTileCtas : 0), C1_GROUPS), dim3(C1_THREADS), 0, s, a1, pdl && c->chained_step);
   mark();
   // 2. BN1 + ReLU + pool
   BnPoolArgs b1{c->y1, c->p1, c->use_tc ? c->p1h : nullptr, c->params, st1, c->bnbuf, c->nbt, c->ds, c->comm, B, 0, 0, sync, cfg.bn_momentum, cfg.bn_eps,
@@ -949,6 +961,80 @@ extern "C" int ddpstep_train_step(ddpstep_ctx* ctx, const float* x, const int64_
   return rc;
 }
 
+// K consecutive iterations of train() (ddp_main.py:85-93) as ONE graph launch: the steps are chained inside the graph by
+// programmatic edges (the next step's conv1 is resident and waiting while the tail kernel of the current one runs), so
+// the ~3 us between two graph launches and the host's launch jitter -- at world > 1 the first exchange of every step
+// absorbs the slowest rank's -- are paid once per K steps instead of once per step.  The batches are copied (device to
+// device, stream-ordered) into staging buffers of the library, so the captured graph is replayed for any pointers.
+//   kind 0: x_dev [K*batch, 784] fp32 + y_dev [K*batch] int64, K consecutive batches
+//   kind 1: uint8 dataset + labels + idx_dev [K*batch] sampler indices (a whole epoch segment per call)
+static int run_multi(ddpstep_ctx* ctx, int kind, const void* data, const int64_t* labels, const int64_t* idx, int K, int B,
+                     cudaStream_t s) {
+  if (K < 1 || K > 4096) return fail(ctx, DDPSTEP_E_ARG, "n_steps %d outside [1, 4096]", K);
+  if (!ctx->cfg.use_graph) return fail(ctx, DDPSTEP_E_STATE, "multi-step launches need use_graph = 1");
+  const size_t need = (size_t)K * B;
+  if (need > ctx->multi_cap) {  // lazily sized staging: allocation happens outside any capture, old graphs are dropped
+    CK(cudaStreamSynchronize(s));
+    for (auto& kv : ctx->multi_graphs) { cudaGraphExecDestroy(kv.second.exec); cudaGraphDestroy(kv.second.graph); }
+    ctx->multi_graphs.clear();
+    cudaFree(ctx->xs_stage); cudaFree(ctx->ys_stage); cudaFree(ctx->idx_stage);
+    ctx->xs_stage = nullptr; ctx->ys_stage = nullptr; ctx->idx_stage = nullptr; ctx->multi_cap = 0;
+    CK(cudaMalloc(&ctx->xs_stage, need * 784 * 4));
+    CK(cudaMalloc(&ctx->ys_stage, need * 8));
+    CK(cudaMalloc(&ctx->idx_stage, need * 8));
+    ctx->multi_cap = need;
+  }
+  if (kind == 0) {
+    CK(cudaMemcpyAsync(ctx->xs_stage, data, need * 784 * 4, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemcpyAsync(ctx->ys_stage, labels, need * 8, cudaMemcpyDeviceToDevice, s));
+  } else {
+    CK(cudaMemcpyAsync(ctx->idx_stage, idx, need * 8, cudaMemcpyDeviceToDevice, s));
+  }
+  const auto key = std::make_tuple(kind, K, B, kind == 0 ? (const void*)nullptr : data, kind == 0 ? (const void*)nullptr : (const void*)labels);
+  auto it = ctx->multi_graphs.find(key);
+  if (it == ctx->multi_graphs.end()) {
+    GraphEntry ge;
+    Recorder rec;
+    const int64_t before = ctx->launches;
+    CK(cudaStreamBeginCapture(ctx->cap_stream, cudaStreamCaptureModeThreadLocal));
+    cudaError_t e = cudaSuccess;
+    for (int k = 0; k < K && e == cudaSuccess; ++k) {
+      ctx->chained_step = k > 0;
+      const BatchSrc src = kind == 0 ? BatchSrc{ctx->xs_stage + (size_t)k * B * 784, nullptr, nullptr}
+                                     : BatchSrc{nullptr, static_cast<const unsigned char*>(data), ctx->idx_stage + (size_t)k * B};
+      e = enqueue<true>(ctx, src, kind == 0 ? ctx->ys_stage + (size_t)k * B : labels, B, ctx->cap_stream, &rec);
+    }
+    ctx->chained_step = false;
+    cudaError_t e2 = cudaStreamEndCapture(ctx->cap_stream, &ge.graph);
+    ctx->launches = before;
+    if (e != cudaSuccess || e2 != cudaSuccess) {
+      if (ge.graph) cudaGraphDestroy(ge.graph);
+      return fail(ctx, DDPSTEP_E_CUDA, "multi-step graph capture failed: %s", cudaGetErrorString(e != cudaSuccess ? e : e2));
+    }
+    if (cudaError_t e3 = cudaGraphInstantiate(&ge.exec, ge.graph, 0); e3 != cudaSuccess) {
+      cudaGraphDestroy(ge.graph);
+      return fail(ctx, DDPSTEP_E_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e3));
+    }
+    ge.n_kernels = rec.n;
+    ge.planes = ctx->last_planes;
+    it = ctx->multi_graphs.emplace(key, ge).first;
+  }
+  CK(cudaGraphLaunch(it->second.exec, s));
+  ctx->launches += it->second.n_kernels;
+  ctx->last_planes = it->second.planes;
+  ctx->steps_enqueued += (unsigned int)K;
+  return 0;
+}
+
+extern "C" int ddpstep_train_steps(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t n_steps, int32_t batch,
+                                   void* stream) {
+  int rc = check_step_args(ctx, x_dev, batch);
+  if (rc) return rc;
+  if (!y_dev) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  return run_multi(ctx, 0, x_dev, y_dev, nullptr, n_steps, batch, static_cast<cudaStream_t>(stream));
+}
+
 // A micro-step inside `with model.no_sync():` (torch/nn/parallel/distributed.py:1441-1470): forward, loss and
 // backward exactly as ddpstep_train_step -- BN statistics, running buffers and, under SyncBN, their exchanges included --
 // but the local gradient is ADDED to an accumulation buffer (what `.grad` does when zero_grad() is not called) and nothing
@@ -1015,6 +1101,15 @@ extern "C" int ddpstep_eval_batch_indexed(ddpstep_ctx* ctx, const uint8_t* image
   cudaError_t e = enqueue<false>(ctx, src, labels, batch, s, nullptr);
   if (e != cudaSuccess) return fail(ctx, DDPSTEP_E_CUDA, "eval launch failed: %s", cudaGetErrorString(e));
   return 0;
+}
+
+extern "C" int ddpstep_train_steps_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8, const int64_t* labels,
+                                           const int64_t* idx, int32_t n_steps, int32_t batch, void* stream) {
+  int rc = check_indexed(ctx, images_u8, labels, idx, batch);
+  if (rc) return rc;
+  if (!labels) return fail(ctx, DDPSTEP_E_ARG, "null label pointer");
+  CK(cudaSetDevice(ctx->cfg.device));
+  return run_multi(ctx, 1, images_u8, labels, idx, n_steps, batch, static_cast<cudaStream_t>(stream));
 }
 
 // Is this host pointer page-locked and mapped (cudaHostAlloc / cudaHostRegister / torch pin_memory)?  Then

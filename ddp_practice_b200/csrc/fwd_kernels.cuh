@@ -154,8 +154,11 @@ __global__ void __launch_bounds__(C1_THREADS) k_conv1_fwd(Conv1Args a) {
   __shared__ float red[4][8];
   const int tid = threadIdx.x, cg = blockIdx.y;
   T* __restrict__ y1 = reinterpret_cast<T*>(a.y1);
-  const unsigned int ll_tag = (unsigned int)a.ds->epoch + 1u;  // needed only at the very end: fetched now
-  pdl_sync();  // first kernel of the step: nothing to wait for, lets the BN kernel start its prologue
+  // First kernel of the step.  Alone in its graph it has nothing to wait for; in a multi-step graph
+  // (ddpstep_train_steps) its programmatic predecessor is the PREVIOUS step's tail kernel, which writes the parameters
+  // and the step counter -- so both are read only after the wait.
+  pdl_sync();
+  const unsigned int ll_tag = (unsigned int)a.ds->epoch + 1u;
   if (a.w2_tiles != nullptr && (int)blockIdx.x >= a.conv_ctas) {
     w2_tile_gather<T>(a.params, a.w2_tiles, (((int)blockIdx.x - a.conv_ctas) * C1_GROUPS + cg) * C1_THREADS + tid);
     return;

@@ -145,6 +145,20 @@ class Engine:
         assert y.is_cuda and y.dtype == torch.int64 and y.is_contiguous()
         self._check(self.lib.ddpstep_train_step(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0], self._stream()))
 
+    def train_steps(self, x: torch.Tensor, y: torch.Tensor, batch: int):
+        """x.shape[0] // batch consecutive training steps on device-resident batches as ONE graph launch."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous() and x.shape[0] % batch == 0
+        assert y.is_cuda and y.dtype == torch.int64 and y.is_contiguous() and y.shape[0] == x.shape[0]
+        self._check(self.lib.ddpstep_train_steps(self.ctx, x.data_ptr(), y.data_ptr(), x.shape[0] // batch, batch, self._stream()))
+
+    def train_steps_indexed(self, images_u8: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor, batch: int):
+        """An epoch segment: idx holds the sampler's indices of idx.shape[0] // batch full batches; one graph launch."""
+        assert images_u8.is_cuda and images_u8.dtype == torch.uint8 and images_u8.is_contiguous()
+        assert labels.is_cuda and labels.dtype == torch.int64 and idx.is_cuda and idx.dtype == torch.int64
+        assert idx.is_contiguous() and idx.shape[0] % batch == 0
+        self._check(self.lib.ddpstep_train_steps_indexed(self.ctx, images_u8.data_ptr(), labels.data_ptr(), idx.data_ptr(),
+                                                         idx.shape[0] // batch, batch, self._stream()))
+
     def train_step_accumulate(self, x: torch.Tensor, y: torch.Tensor):
         """A micro-step inside `with model.no_sync():` -- forward + backward, the gradient accumulated locally."""
         assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()

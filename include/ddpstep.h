@@ -122,6 +122,14 @@ int ddpstep_state_ptrs(ddpstep_ctx* ctx, ddpstep_ptrs* out);
  * graph replay.  x: [batch,1,28,28] fp32, y: [batch] int64, both DEVICE pointers.          */
 int ddpstep_train_step(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t batch,
                        void* stream);
+/* K consecutive iterations of train() (the `for images, labels in train_dloader` loop of
+ * ddp_main.py:85-93) as ONE graph launch.  x_dev [n_steps*batch,1,28,28] fp32 and y_dev
+ * [n_steps*batch] int64 hold n_steps consecutive batches on the device.  Identical arithmetic
+ * and state to n_steps calls of ddpstep_train_step; inside the graph the steps are chained by
+ * programmatic edges, so the gap between two graph launches and the host's launch jitter (which
+ * at world > 1 the first exchange of every step has to absorb) are paid once per call.          */
+int ddpstep_train_steps(ddpstep_ctx* ctx, const float* x_dev, const int64_t* y_dev, int32_t n_steps,
+                        int32_t batch, void* stream);
 /* One iteration inside `with model.no_sync():` -- gradient accumulation, SURVEY.md 8(f) N3
  * (torch/nn/parallel/distributed.py:1441-1470; the reference never uses it): forward, loss and
  * backward as in ddpstep_train_step (BN statistics, running buffers and SyncBN exchanges
@@ -148,6 +156,10 @@ int ddpstep_train_step_host(ddpstep_ctx* ctx, const float* x_host, const int64_t
  * conv1's load.  Same arithmetic, bit for bit, as ddpstep_train_step on images_u8[idx].float() / 255.        */
 int ddpstep_train_step_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8_dev, const int64_t* labels_dev,
                                const int64_t* idx_dev, int32_t batch, void* stream);
+/* ... and an epoch segment of it in one launch: idx_dev holds n_steps*batch sampler indices
+ * (what `train_dloader.sampler` yields after set_epoch, ddp_main.py:160), n_steps full batches.  */
+int ddpstep_train_steps_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8_dev, const int64_t* labels_dev,
+                                const int64_t* idx_dev, int32_t n_steps, int32_t batch, void* stream);
 int ddpstep_eval_batch_indexed(ddpstep_ctx* ctx, const uint8_t* images_u8_dev, const int64_t* labels_dev,
                                const int64_t* idx_dev, int32_t batch, void* stream);
 

@@ -291,6 +291,46 @@ def test_graph_replay_equals_eager_launches_and_is_deterministic():
         assert o[3] == outs[0][3]
 
 
+@pytest.mark.parametrize("dtype,batch", [("fp16", 32), ("bf16", 12), ("fp32", 32), ("fp16", 80)])
+def test_multi_step_graph_equals_single_step_launches(dtype, batch):
+    """ddpstep_train_steps / _indexed: K steps chained inside one graph (programmatic edge from a step's tail kernel to the
+    next step's conv1) must leave exactly the state K single-step launches leave -- bit for bit -- also when replayed
+    with other data and after a single-step call in between."""
+    st = _seed_state()
+    K = 5
+    x, y = O.synthetic_mnist(batch * K * 2)
+    u8h = (x * 255).round().to(torch.uint8)
+    u8 = u8h.cuda().contiguous()
+    # ToTensor's division on the CPU, as the reference's pipeline does it (torch's CUDA division by a scalar multiplies by
+    # the reciprocal instead, which differs in the last fp32 bit for some bytes)
+    xd, yd = (u8h.float() / 255).cuda().contiguous(), y.cuda().contiguous()
+    perm = torch.randperm(batch * K * 2, generator=torch.Generator().manual_seed(1)).cuda()
+    a, b, c = (_engine(dtype=dtype, batch_cap=batch, use_scaler=dtype != "fp32") for _ in range(3))
+    for e in (a, b, c):
+        e.load_state(st.flat_params().numpy(), _bn_of(st))
+    for rep in range(2):
+        lo = rep * K * batch
+        for k in range(K):
+            a.train_step(xd[lo + k * batch: lo + (k + 1) * batch], yd[lo + k * batch: lo + (k + 1) * batch])
+        b.train_steps(xd[lo: lo + K * batch], yd[lo: lo + K * batch], batch)
+        c.train_steps_indexed(u8, yd, torch.arange(lo, lo + K * batch, device="cuda"), batch)
+        torch.cuda.synchronize()
+        for e in (b, c):
+            assert torch.equal(a.params.view(torch.int32), e.params.view(torch.int32)), f"rep {rep}"
+            assert torch.equal(a.bn_buffers, e.bn_buffers) and torch.equal(a.grads.view(torch.int32), e.grads.view(torch.int32))
+            assert (a.scale.item(), a.growth_tracker.item(), a.loss.item()) == (e.scale.item(), e.growth_tracker.item(), e.loss.item())
+            assert a.num_batches_tracked.tolist() == e.num_batches_tracked.tolist()
+            assert a.launch_count() == e.launch_count()
+    # shuffled indices, as a DistributedSampler would hand them over
+    a.train_step(xd[perm[:batch]].contiguous(), yd[perm[:batch]].contiguous())
+    a.train_step(xd[perm[batch:2 * batch]].contiguous(), yd[perm[batch:2 * batch]].contiguous())
+    c.train_steps_indexed(u8, yd, perm[:2 * batch].contiguous(), batch)
+    torch.cuda.synchronize()
+    assert torch.equal(a.params.view(torch.int32), c.params.view(torch.int32))
+    for e in (a, b, c):
+        e.close()
+
+
 def test_host_entry_point_equals_device_entry_point():
     st = _seed_state()
     x, y = O.synthetic_mnist(64)
