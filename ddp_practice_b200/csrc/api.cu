@@ -93,6 +93,8 @@ struct ddpstep_ctx {
   cudaEvent_t ev_h0 = nullptr, ev_h1 = nullptr, ev_m = nullptr;
   float* gred = nullptr;
   float* mom = nullptr;   // SGD momentum buffers, same flat layout as the parameters
+  llword* tail_flags = nullptr;  // per-CTA flag words of the grid-shaped tail kernel
+  bool tail_grid = true;  // tail kernel as 29 ordinary CTAs (default) or as one 8-CTA cluster (DDPSTEP_TAIL=cluster)
   float* acc = nullptr;   // gradient accumulated by DDP.no_sync() micro-steps, same layout
   bool accumulate = false;  // the step being enqueued is such a micro-step
   volatile float* host_mail = nullptr;  // pinned, mapped: {loss, completed-step counter}
@@ -183,7 +185,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   A(part1, 296 * 16 * 2 * 4); A(part2, 296 * 32 * 2 * 4); A(bpart, 32 * 32 * 2 * 4);
   A(part1_ll, 64 * 32 * 8); A(part2_ll, 64 * 64 * 8); A(bpart1_ll, 16 * 64 * 2 * 8); A(bpart2_ll, 32 * 64 * 2 * 8);
   A(gpart, (size_t)MAX_PART_ROWS * N_PAD * 4); A(gdirect, N_PAD * 4);
-  A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4); A(mom, N_PAD * 4); A(acc, N_PAD * 4);
+  A(x_stage, B * 784 * 4); A(y_stage, B * 8); A(gred, N_PAD * 4); A(mom, N_PAD * 4); A(acc, N_PAD * 4); A(tail_flags, 64 * 8);
   {
     const char* env = getenv("DDPSTEP_TC");
     ctx->use_tc = cfg->dtype != DDPSTEP_FP32 && !(env && env[0] == '0');
@@ -195,6 +197,8 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
     ctx->use_pdl = !(envp && envp[0] == '0');
     const char* envd = getenv("DDPSTEP_DEFER");
     if (envd && envd[0] >= '0' && envd[0] <= '2') ctx->defer_stats = envd[0] - '0';
+    const char* envt = getenv("DDPSTEP_TAIL");
+    ctx->tail_grid = !(envt && envt[0] == 'c');
     const char* enve = getenv("DDPSTEP_EARLY_PUSH");
     ctx->early_push = !(enve && enve[0] == '0');
     const char* envm = getenv("DDPSTEP_MID");
@@ -313,7 +317,7 @@ extern "C" int ddpstep_destroy(ddpstep_ctx* ctx) {
                   ctx->nll, ctx->part1, ctx->part2, ctx->bpart, ctx->gpart, ctx->gdirect, ctx->x_stage,
                   ctx->y_stage, ctx->sym, ctx->p1h, ctx->dy2h, ctx->w2_tiles, ctx->gred,
                   ctx->part1_ll, ctx->part2_ll, ctx->bpart1_ll, ctx->bpart2_ll, ctx->mom, ctx->acc,
-                  ctx->xs_stage, ctx->ys_stage, ctx->idx_stage};
+                  ctx->xs_stage, ctx->ys_stage, ctx->idx_stage, ctx->tail_flags};
   for (void* p : bufs) if (p) cudaFree(p);
   if (ctx->host_mail) cudaFreeHost(const_cast<float*>(ctx->host_mail));
   if (ctx->cap_stream) cudaStreamDestroy(ctx->cap_stream);
@@ -686,10 +690,12 @@ static cudaError_t enqueue_train(ddpstep_ctx* c, const BatchSrc& x, const int64_
   // 13. Reducer all-reduce + GradScaler + SGD
   StepArgs sa{c->params, c->grads, c->grads_scaled, c->gpart, c->gred, c->gdirect, c->nll, c->host_mail, c->bnbuf, c->nbt, c->ds, c->comm, B,
               rows_c1, gw_rows, mid ? 0 : (planes ? ns2p : ns2), nsf, cfg.use_scaler, sync, cfg.growth_factor, cfg.backoff_factor, cfg.growth_interval,
-              c->mom, c->post_loss ? 1 : 0, c->acc, c->accumulate ? 1 : 0, early};
+              c->mom, c->post_loss ? 1 : 0, c->acc, c->accumulate ? 1 : 0, c->tail_flags, early};
   if (!c->accumulate) { c->last_step = sa; c->last_step_dtype_ok = 1; }
   if (fork) { cudaStreamWaitEvent(s, c->ev_j1, 0); cudaStreamWaitEvent(s, c->ev_j2, 0); }
-  launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl); mark();
+  if (c->tail_grid) launch_k(k_step_grid<T>, dim3(STEP_GRID_CTAS), dim3(STEP_GRID_THREADS), 0, s, sa, pdl);
+  else launch_k(k_step<T>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, pdl);
+  mark();
   return cudaGetLastError();
 }
 
@@ -1400,13 +1406,19 @@ extern "C" int ddpstep_allreduce_only(ddpstep_ctx* ctx, void* stream) {
   switch (ctx->cfg.dtype) {
     case DDPSTEP_FP32:
       if (sa.early_push) { k_fc_reduce_push<float><<<nfc, 128, 0, s>>>(ctx->last_push_fc); k_reduce_rows<float><<<nc2, 128, 0, s>>>(ctx->last_push_c2); }
-      launch_k(k_step<float>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+      if (ctx->tail_grid) launch_k(k_step_grid<float>, dim3(STEP_GRID_CTAS), dim3(STEP_GRID_THREADS), 0, s, sa, false);
+      else launch_k(k_step<float>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false);
+      break;
     case DDPSTEP_FP16:
       if (sa.early_push) { k_fc_reduce_push<__half><<<nfc, 128, 0, s>>>(ctx->last_push_fc); k_reduce_rows<__half><<<nc2, 128, 0, s>>>(ctx->last_push_c2); }
-      launch_k(k_step<__half>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+      if (ctx->tail_grid) launch_k(k_step_grid<__half>, dim3(STEP_GRID_CTAS), dim3(STEP_GRID_THREADS), 0, s, sa, false);
+      else launch_k(k_step<__half>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false);
+      break;
     default:
       if (sa.early_push) { k_fc_reduce_push<__nv_bfloat16><<<nfc, 128, 0, s>>>(ctx->last_push_fc); k_reduce_rows<__nv_bfloat16><<<nc2, 128, 0, s>>>(ctx->last_push_c2); }
-      launch_k(k_step<__nv_bfloat16>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false); break;
+      if (ctx->tail_grid) launch_k(k_step_grid<__nv_bfloat16>, dim3(STEP_GRID_CTAS), dim3(STEP_GRID_THREADS), 0, s, sa, false);
+      else launch_k(k_step<__nv_bfloat16>, dim3(STEP_CTAS), dim3(STEP_THREADS), 0, s, sa, false);
+      break;
   }
   CK(cudaGetLastError());
   ctx->launches += sa.early_push ? 3 : 1;

@@ -46,6 +46,7 @@ struct StepArgs {
   int post_loss;  // 1: post {loss, step counter} to host_mail (ddpstep_train_step_host polls it)
   float* acc;     // [N_PAD] accumulation buffer of DDP.no_sync() micro-steps
   int accumulate; // 1: micro-step inside no_sync(): add the local gradient to `acc`, exchange / apply nothing
+  llword* tail_flags;  // [32] per-CTA flag words of the non-cluster launch shape (k_step_grid)
   int early_push; // world > 1: the conv2-filter and Linear slices were pushed by the side branches (k_reduce_rows,
                   // k_fc_reduce_push); this kernel only gathers them
 };
@@ -145,14 +146,26 @@ __global__ void __launch_bounds__(256) k_refresh_w2_tiles(const float* __restric
   w2_tile_gather<T>(params, tiles, blockIdx.x * 256 + threadIdx.x);  // one thread per tile element, coalesced stores
 }
 
-template <typename T>
-__global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS) k_step(StepArgs a) {
+// Two launch shapes share this body:
+//   CLUSTER = true : one 8-CTA cluster of 1024 threads; the step-wide flags (non-finite, peer timeout) travel through
+//                    distributed shared memory and one cluster barrier.  Needs 8 completely free SMs at once.
+//   CLUSTER = false: 29 ordinary CTAs of 256 threads; every CTA publishes its flags as one tagged word in global memory and
+//                    polls the others' (one L2 round trip).  Small CTAs fit beside the still-running predecessor
+//                    kernels, so under programmatic launch the tail is resident early instead of waiting for eight
+//                    whole SMs to drain -- which is what delayed it by ~3 us at world 8, where the predecessor's CTAs
+//                    spin on a cross-GPU exchange (profiles/r02_trace_b32_w8.txt).
+constexpr int STEP_GRID_THREADS = 256;
+constexpr int STEP_GRID_CTAS = (N_PAD + STEP_GRID_THREADS * 4 - 1) / (STEP_GRID_THREADS * 4);  // 29
+
+template <typename T, int NTHREADS, bool CLUSTER>
+__device__ __forceinline__ void step_body(const StepArgs& a) {
   if (threadIdx.x == 0) TRACE(13 * 16 + 0);
-  cg::cluster_group cluster = cg::this_cluster();
+  constexpr int LANES = NTHREADS / 104;           // row lanes of the cooperative conv1-region sum (9 or 2)
+  constexpr int PER = LANES >= 8 ? 4 : 16;        // loads in flight per lane and trip to L2
   __shared__ int s_nonfinite;
   __shared__ int s_flags[STEP_CTAS];
   const int tid = threadIdx.x, cta = blockIdx.x;
-  const int e = (cta * STEP_THREADS + tid) * 4;
+  const int e = (cta * NTHREADS + tid) * 4;
   const bool valid = e < N_PARAM;  // last float4 (29032..29035) is half padding
   const int W = a.comm.world, rank = a.comm.rank;
   const unsigned long long epoch = a.ds->epoch, sync_epoch = a.ds->sync_epoch;
@@ -176,7 +189,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   // CTA 0 owns the conv1 region (elements 0..415), whose gradient arrives as one partial row per
   // conv1-wgrad CTA: all 1024 threads sum it together (9 row lanes per float4, one round trip to
   // L2 instead of rows/8), fixed order.  Warp 0 also fetches the per-image losses now.
-  __shared__ float4 s_c1[9][104];
+  __shared__ float4 s_c1[LANES][104];
   float nll_pref = 0.f;
   // CTA 0's other elements (BN affine gradients, the head of conv2's filter) need one row each: that load is issued
   // before the cooperative sum so both travel to L2 together
@@ -187,18 +200,18 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   if (pre_red) pre = __ldcg(reinterpret_cast<const float4*>(a.gred + e));
   if (cta == 0) {
     const int e4 = tid % 104, rl = tid / 104;
-    if (rl < 9) {
-      // four predicated loads per trip, never a one-load-at-a-time remainder loop (a partially unrolled loop with
+    if (rl < LANES) {
+      // PER predicated loads per trip, never a one-load-at-a-time remainder loop (a partially unrolled loop with
       // a run-time trip count gets one, and each of its loads is a full trip to L2)
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int r0 = rl; r0 < a.rows_conv1; r0 += 36) {
-        float4 v[4];
+      for (int r0 = rl; r0 < a.rows_conv1; r0 += PER * LANES) {
+        float4 v[PER];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          v[i] = r0 + 9 * i < a.rows_conv1 ? __ldcg(reinterpret_cast<const float4*>(a.gpart + (size_t)(r0 + 9 * i) * N_PAD + 4 * e4))
-                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int i = 0; i < PER; ++i)
+          v[i] = r0 + LANES * i < a.rows_conv1 ? __ldcg(reinterpret_cast<const float4*>(a.gpart + (size_t)(r0 + LANES * i) * N_PAD + 4 * e4))
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) { acc.x += v[i].x; acc.y += v[i].y; acc.z += v[i].z; acc.w += v[i].w; }
+        for (int i = 0; i < PER; ++i) { acc.x += v[i].x; acc.y += v[i].y; acc.z += v[i].z; acc.w += v[i].w; }
       }
       s_c1[rl][e4] = acc;
     }
@@ -229,7 +242,7 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
       if (e < OFF_G1) {  // conv1 region: lanes summed above, combine in fixed order
         rows = 0;
 #pragma unroll
-        for (int l = 0; l < 9; ++l) {
+        for (int l = 0; l < LANES; ++l) {
           const float4 v = s_c1[l][e >> 2];
           g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
         }
@@ -352,12 +365,29 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
   // slot [its rank] of ALL eight CTAs (the cluster is co-scheduled, so remote shared memory exists
   // from the start), ONE cluster barrier, then everybody reads its own eight slots
   __syncthreads();
-  if (tid < STEP_CTAS) *cluster.map_shared_rank(&s_flags[cta], tid) = s_nonfinite;
-  cluster.sync();
-  if (threadIdx.x == 0) TRACE(13 * 16 + 4);
   int flags = 0;
+  if constexpr (CLUSTER) {
+    cg::cluster_group cluster = cg::this_cluster();
+    if (tid < STEP_CTAS) *cluster.map_shared_rank(&s_flags[cta], tid) = s_nonfinite;
+    cluster.sync();
 #pragma unroll
-  for (int r = 0; r < STEP_CTAS; ++r) flags |= s_flags[r];
+    for (int r = 0; r < STEP_CTAS; ++r) flags |= s_flags[r];
+  } else {
+    // every CTA publishes {flags, step tag} as one 8-byte word; warp 0 polls all of them (the loads of a polling round
+    // are in flight together), ORs them and hands the result to the CTA.  The tag (epoch + 1) is never reused.
+    const unsigned int ftag = (unsigned int)epoch + 1u;
+    if (tid == 0) ll_store(&a.tail_flags[cta], __int_as_float(s_nonfinite), ftag);
+    if (tid < 32) {
+      int f = 0;
+      if (tid < (int)gridDim.x) f = __float_as_int(ll_wait(&a.tail_flags[tid], ftag, a.ds));
+      f = __reduce_or_sync(0xffffffffu, (unsigned int)f);
+      if (*reinterpret_cast<volatile int*>(&a.ds->error) != 0) f |= 2;  // the poll itself timed out
+      if (tid == 0) s_flags[0] = f;
+    }
+    __syncthreads();
+    flags = s_flags[0];
+  }
+  if (threadIdx.x == 0) TRACE(13 * 16 + 4);
   // bit 1: a peer did not answer in time somewhere in this step.  The gradient is then not the all-reduced one: the
   // step applies NOTHING (parameters, momentum, scaler state stay as they were) and tells the host (DDPSTEP_E_PEER).
   const bool dead = (flags & 2) != 0;
@@ -449,6 +479,15 @@ __global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS
     }
   }
   if (threadIdx.x == 0) TRACE(13 * 16 + 15);
+}
+
+template <typename T>
+__global__ void __cluster_dims__(STEP_CTAS, 1, 1) __launch_bounds__(STEP_THREADS) k_step(StepArgs a) {
+  step_body<T, STEP_THREADS, true>(a);
+}
+template <typename T>
+__global__ void __launch_bounds__(STEP_GRID_THREADS) k_step_grid(StepArgs a) {
+  step_body<T, STEP_GRID_THREADS, false>(a);
 }
 
 // ---------------------------------------------------------------------------------------

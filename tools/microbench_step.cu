@@ -35,7 +35,7 @@ int main() {
   };
   for (auto& v : vs) {
     StepArgs a{params, grads, gs, gpart, v.red ? gred : nullptr, gdirect, nll, nullptr, bnbuf, nbt, ds, comm, 32,
-               v.r1, v.r2w, v.r2b, v.rfc, 1, 1, 2.f, 0.5f, 2000, nullptr, 0, nullptr, 0, 0};
+               v.r1, v.r2w, v.r2b, v.rfc, 1, 1, 2.f, 0.5f, 2000, nullptr, 0, nullptr, 0, nullptr, 0};
     float us = time_graph([&](cudaStream_t s) { k_step<__half><<<STEP_CTAS, STEP_THREADS, 0, s>>>(a); }, 8, 500);
     printf("%-42s : %.2f us\n", v.name, us);
   }
