@@ -224,3 +224,29 @@ def test_shim_lr_scheduler_and_no_sync_keep_one_context():
     assert len(engines) == 1, "the native context was rebuilt"
     assert optimizer.param_groups[0]["lr"] == pytest.approx(1e-2 * 0.5 ** 4)
     e.close()
+
+
+def test_torch_ops_are_registered_with_the_dispatcher_and_match_the_engine():
+    """north_star: "delivered as a PyTorch ... extension behind a thin C-ABI" -- torch.ops.ddp_b200.* (torch.library) over
+    the same C ABI: same bits as driving the Engine directly."""
+    from ddp_practice_b200 import Engine, torch_ops
+    torch.manual_seed(3407)
+    m = RefConvNet(torch.float16, "cuda")
+    a, b = Engine(dtype="fp16", batch_cap=32), Engine(dtype="fp16", batch_cap=32)
+    for e in (a, b):
+        e.load_state(flat_params(m).numpy(), bn_buffers(m).numpy())
+    h = torch_ops.register(b)
+    assert "ddp_b200::train_step" in torch._C._dispatch_get_all_op_names()
+    x, y = O.synthetic_mnist(96)
+    x, y = x.cuda(), y.cuda()
+    for s in range(3):
+        a.train_step(x[32 * s:32 * s + 32].contiguous(), y[32 * s:32 * s + 32].contiguous())
+        loss = torch.ops.ddp_b200.train_step(x[32 * s:32 * s + 32], y[32 * s:32 * s + 32], h)
+    torch.cuda.synchronize()
+    assert loss.item() == a.loss.item() and torch.equal(a.params, b.params)
+    lg = torch.ops.ddp_b200.eval_batch(x[:32], h)
+    assert torch.equal(lg, a.eval_batch(x[:32].contiguous()))
+    t = torch.arange(10, dtype=torch.float32, device="cuda")
+    assert torch.equal(torch.ops.ddp_b200.allreduce_bucket_(t, h), torch.arange(10, dtype=torch.float32, device="cuda"))
+    torch_ops.unregister(h)
+    a.close(); b.close()
