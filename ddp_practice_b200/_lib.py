@@ -58,6 +58,7 @@ SYMBOLS = [
     ("ddpstep_kernel_name", C.c_char_p, [C.c_int32]),
     ("ddpstep_conv1_bnstats_noalloc", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P, _P, _P]),
     ("ddpstep_set_sgd", C.c_int, [_P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int32, _P]),
+    ("ddpstep_set_sgd_group", C.c_int, [_P, C.c_uint32, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int32, _P]),
     ("ddpstep_set_peer_timeout_ms", C.c_int, [_P, C.c_double]),
     ("ddpstep_allreduce_only", C.c_int, [_P, _P]),
     ("ddpstep_allreduce_bucket", C.c_int, [_P, _P, C.c_int64, C.c_int32, _P]),

@@ -103,6 +103,7 @@ struct ddpstep_ctx {
   bool chained_step = false;           // the step being enqueued follows another one inside the same captured graph
   float* xs_stage = nullptr; int64_t* ys_stage = nullptr; long long* idx_stage = nullptr;  // multi-step staging (lazy)
   size_t multi_cap = 0;                // images the multi-step staging buffers hold
+  DevState::SgdGroup groups[10];       // host copies of the per-tensor SGD settings (source of the async uploads)
   bool post_loss = false;              // the step being enqueued posts its loss to the pinned mailbox (host entry point)
   int sm_khz = 1965000;                // SM clock used to turn the peer timeout into clock64() cycles
   StepArgs last_step;                  // arguments of the most recently enqueued tail kernel (ddpstep_allreduce_only)
@@ -219,8 +220,7 @@ extern "C" int ddpstep_create(const ddpstep_config* cfg, ddpstep_ctx** out) {
   DevState h;
   memset(&h, 0, sizeof h);
   h.scale = cfg->use_scaler ? cfg->init_scale : 1.0f;
-  h.lr = cfg->lr; h.momentum = cfg->momentum; h.weight_decay = cfg->weight_decay; h.dampening = cfg->dampening;
-  h.nesterov = cfg->nesterov;
+  for (int t = 0; t < 10; ++t) h.grp[t] = {cfg->lr, cfg->momentum, cfg->weight_decay, cfg->dampening, cfg->nesterov};
   ctx->sm_khz = prop.clockRate > 0 ? prop.clockRate : 1965000;
   {
     // default peer timeout: 20 s (a rank may legitimately be seconds late: first-batch DataLoader start, a rank-0
@@ -1335,20 +1335,33 @@ extern "C" int ddpstep_device_status(ddpstep_ctx* ctx) {
 // memory, so neither the context nor any captured graph has to be rebuilt.  Stream-ordered: steps enqueued after this
 // call on the same stream use the new values.  ddp_main.py:125 sets them once; torch/optim/sgd.py:425-465 reads them
 // every step.
-extern "C" int ddpstep_set_sgd(ddpstep_ctx* ctx, float lr, float momentum, float weight_decay, float dampening, int32_t nesterov,
-                               void* stream) {
+extern "C" int ddpstep_set_sgd_group(ddpstep_ctx* ctx, uint32_t tensor_mask, float lr, float momentum, float weight_decay,
+                                     float dampening, int32_t nesterov, void* stream) {
   if (!ctx) return DDPSTEP_E_ARG;
+  if ((tensor_mask & 0x3FFu) == 0 || (tensor_mask & ~0x3FFu))
+    return fail(ctx, DDPSTEP_E_ARG, "tensor_mask must select some of the 10 parameter tensors (bits 0..9)");
   if (momentum < 0.f || weight_decay < 0.f) return fail(ctx, DDPSTEP_E_ARG, "momentum and weight_decay must be >= 0");
   if (nesterov && (momentum <= 0.f || dampening != 0.f))
     return fail(ctx, DDPSTEP_E_ARG, "nesterov momentum requires a momentum and zero dampening");  // sgd.py:68
   CK(cudaSetDevice(ctx->cfg.device));
-  struct { float lr, momentum, weight_decay, dampening; int nesterov; } h = {lr, momentum, weight_decay, dampening, nesterov ? 1 : 0};
-  static_assert(offsetof(DevState, nesterov) - offsetof(DevState, lr) == 16, "DevState hyper-parameter block");
-  // pageable source: the runtime stages it before returning, so `h` may go out of scope
-  CK(cudaMemcpyAsync(&ctx->ds->lr, &h, sizeof h, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
-  ctx->cfg.lr = lr; ctx->cfg.momentum = momentum; ctx->cfg.weight_decay = weight_decay; ctx->cfg.dampening = dampening;
-  ctx->cfg.nesterov = nesterov ? 1 : 0;
+  const DevState::SgdGroup g = {lr, momentum, weight_decay, dampening, nesterov ? 1 : 0};
+  for (int t = 0; t < 10; ++t)
+    if (tensor_mask >> t & 1u) {
+      ctx->groups[t] = g;
+      // pageable source: the runtime stages it before returning
+      CK(cudaMemcpyAsync(&ctx->ds->grp[t], &ctx->groups[t], sizeof g, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+    }
   return 0;
+}
+
+extern "C" int ddpstep_set_sgd(ddpstep_ctx* ctx, float lr, float momentum, float weight_decay, float dampening, int32_t nesterov,
+                               void* stream) {
+  int rc = ddpstep_set_sgd_group(ctx, 0x3FFu, lr, momentum, weight_decay, dampening, nesterov, stream);
+  if (rc == 0) {
+    ctx->cfg.lr = lr; ctx->cfg.momentum = momentum; ctx->cfg.weight_decay = weight_decay; ctx->cfg.dampening = dampening;
+    ctx->cfg.nesterov = nesterov ? 1 : 0;
+  }
+  return rc;
 }
 
 // DDP communication-hook work for one GradBucket of any model (SURVEY 8b alternative B, 8f N3): bucket <- sum over

@@ -16,6 +16,13 @@ constexpr int OFF_WFC = 13344, OFF_BFC = 29024;
 // BN buffer block: rm1[16] rv1[16] rm2[32] rv2[32]
 constexpr int BNB_RM1 = 0, BNB_RV1 = 16, BNB_RM2 = 32, BNB_RV2 = 64, N_BNBUF = 96;
 
+// which of the ten parameter tensors element e of the flat vector belongs to (every float4 lies inside one tensor:
+// all offsets are multiples of 4)
+__host__ __device__ __forceinline__ int tensor_of(int e) {
+  return (e >= OFF_B1) + (e >= OFF_G1) + (e >= OFF_BE1) + (e >= OFF_W2) + (e >= OFF_B2) + (e >= OFF_G2) + (e >= OFF_BE2) +
+         (e >= OFF_WFC) + (e >= OFF_BFC);
+}
+
 constexpr int MAX_WORLD = 8;
 constexpr int STEP_CTAS = 8;        // one cluster
 constexpr int STEP_THREADS = 1024;  // 8 * 1024 * 4 = 32768 >= N_PAD
@@ -102,8 +109,10 @@ struct DevState {
   // Run-time hyper-parameters of torch.optim.SGD (param_groups[0]; sgd.py:425-465).  They live in device memory, not in
   // kernel arguments, so an LR scheduler or a hand-edited param group changes them without a new context or graph
   // (ddpstep_set_sgd).
-  float lr, momentum, weight_decay, dampening;
-  int nesterov;
+  // One entry per parameter tensor in definition order (conv1.w, conv1.b, bn1.g, bn1.b, conv2.w, conv2.b, bn2.g, bn2.b,
+  // fc.w, fc.b), so that optimizer.param_groups with different settings are expressible (ddpstep_set_sgd_group);
+  // ddpstep_set_sgd writes all ten.
+  struct SgdGroup { float lr, momentum, weight_decay, dampening; int nesterov; } grp[10];
   // Cross-rank waits give up after this many SM clock cycles (ddpstep_set_peer_timeout_ms) and raise `error`; a step
   // that saw the error applies no update (k_step) and the host API reports DDPSTEP_E_PEER.
   long long timeout_cycles;

@@ -173,8 +173,10 @@ __device__ __forceinline__ void step_body(const StepArgs& a) {
   const float scale = a.ds->scale;
   const int tracker = a.ds->growth_tracker;
   const int mom_ready = a.ds->mom_ready;
-  const float lr = a.ds->lr, momentum = a.ds->momentum, weight_decay = a.ds->weight_decay, dampening = a.ds->dampening;
-  const int nesterov = a.ds->nesterov;
+  // this thread's four elements belong to one parameter tensor; its param group's settings (torch/optim/sgd.py:425-465)
+  const DevState::SgdGroup grp = a.ds->grp[tensor_of(min(e, N_PARAM - 1))];
+  const float lr = grp.lr, momentum = grp.momentum, weight_decay = grp.weight_decay, dampening = grp.dampening;
+  const int nesterov = grp.nesterov;
   if (tid == 0) s_nonfinite = 0;
   // parameters are fetched now, long before they are needed, so the load overlaps everything below
   float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -464,7 +466,11 @@ __device__ __forceinline__ void step_body(const StepArgs& a) {
           }
         }
       }
-      if (!found && momentum != 0.f) a.ds->mom_ready = 1;
+      if (!found) {  // momentum buffers exist from the first executed step of any group that uses momentum
+        bool any = false;
+        for (int t = 0; t < 10; ++t) any = any || a.ds->grp[t].momentum != 0.f;
+        if (any) a.ds->mom_ready = 1;
+      }
       a.ds->epoch = epoch + 1ull;
       a.ds->sync_epoch = sync_epoch + 1ull;
       a.ds->acc_valid = 0;

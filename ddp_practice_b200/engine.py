@@ -240,6 +240,12 @@ class Engine:
         """`optimizer.param_groups[0]` changed (LR scheduler): new values for the steps enqueued from now on."""
         self._check(self.lib.ddpstep_set_sgd(self.ctx, lr, momentum, weight_decay, dampening, int(nesterov), self._stream()))
 
+    def set_sgd_group(self, tensor_mask: int, lr: float, momentum: float = 0.0, weight_decay: float = 0.0,
+                      dampening: float = 0.0, nesterov: bool = False):
+        """One of several `optimizer.param_groups`: bit i of tensor_mask = parameter tensor i in definition order."""
+        self._check(self.lib.ddpstep_set_sgd_group(self.ctx, tensor_mask, lr, momentum, weight_decay, dampening,
+                                                   int(nesterov), self._stream()))
+
     def set_peer_timeout_ms(self, ms: float):
         self._check(self.lib.ddpstep_set_peer_timeout_ms(self.ctx, float(ms)))
 

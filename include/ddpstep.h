@@ -220,6 +220,12 @@ int ddpstep_conv1_bnstats_noalloc(const float* params_dev, const float* x_dev, i
  * enqueued on `stream` after this call use the new values.                                    */
 int ddpstep_set_sgd(ddpstep_ctx* ctx, float lr, float momentum, float weight_decay, float dampening,
                     int32_t nesterov, void* stream);
+/* The same for ONE of several `optimizer.param_groups` (torch/optim/sgd.py:425-465 runs once per
+ * group): tensor_mask selects the parameter tensors of the group, bit i = tensor i in definition
+ * order (0 conv1.weight, 1 conv1.bias, 2 bn1.weight, 3 bn1.bias, 4 conv2.weight, 5 conv2.bias,
+ * 6 bn2.weight, 7 bn2.bias, 8 fc.weight, 9 fc.bias).  ddpstep_set_sgd == mask 0x3FF.  SURVEY 8f N3. */
+int ddpstep_set_sgd_group(ddpstep_ctx* ctx, uint32_t tensor_mask, float lr, float momentum,
+                          float weight_decay, float dampening, int32_t nesterov, void* stream);
 /* How long a kernel polls for a peer's words before giving up (default 20 s; environment
  * DDPSTEP_PEER_TIMEOUT_MS at create time).  The reference's NCCL blocks until its watchdog
  * fires; here the step whose wait expired applies no update and this and

@@ -24,7 +24,7 @@ int main() {
   cudaMalloc(&nll, 4096 * 4); cudaMalloc(&bnbuf, 96 * 4); cudaMalloc(&nbt, 16); cudaMalloc(&ds, sizeof(DevState)); cudaMalloc(&tiles, 51200);
   cudaMemset(params, 0, N_PAD * 4); cudaMemset(gpart, 0, (size_t)160 * N_PAD * 4); cudaMemset(gred, 0, N_PAD * 4);
   cudaMemset(gdirect, 0, N_PAD * 4); cudaMemset(nll, 0, 4096 * 4); cudaMemset(ds, 0, sizeof(DevState));
-  DevState h; memset(&h, 0, sizeof h); h.scale = 32768.f; h.lr = 1e-4f; h.timeout_cycles = 1LL << 40; cudaMemcpy(ds, &h, sizeof h, cudaMemcpyHostToDevice);
+  DevState h; memset(&h, 0, sizeof h); h.scale = 32768.f; for (int t = 0; t < 10; ++t) h.grp[t] = {1e-4f, 0.f, 0.f, 0.f, 0}; h.timeout_cycles = 1LL << 40; cudaMemcpy(ds, &h, sizeof h, cudaMemcpyHostToDevice);
   CommDev comm; memset(&comm, 0, sizeof comm); comm.world = 1;
   struct V { const char* name; int r1, r2w, r2b, rfc; bool red, tl; } vs[] = {
       {"as in the step (rows 32/1/8/4, tiles)", 32, 32, 8, 4, true, true},
