@@ -132,6 +132,7 @@ class DistributedDataParallel(_tnn.Module):
         self._steps = 0
         self._mom_published = False  # optimizer.state[p]['momentum_buffer'] views handed out
         self._no_sync = False
+        self._groups_key = None      # per-tensor settings last sent for an optimizer with several param groups
         self._optimizer = None       # the optimizer seen by the last step (its state holds views of our memory)
         self.last_logits = None
 
@@ -303,6 +304,29 @@ class DistributedDataParallel(_tnn.Module):
         finally:
             self._no_sync = old
 
+    def _apply_param_groups(self, optimizer):
+        """`optimizer.param_groups` with different settings (torch/optim/sgd.py runs its update once per group): every
+        group becomes one `ddpstep_set_sgd_group` call naming its parameter tensors; re-sent only when something changed."""
+        index = {id(p): i for i, (name, _) in enumerate(_SPECS) for p in [dict(self.module.named_parameters())[name]]}
+        groups, seen = [], 0
+        for pg in optimizer.param_groups:
+            mask = 0
+            for p in pg["params"]:
+                if id(p) not in index:
+                    raise RuntimeError("the optimizer holds a parameter that is not one of this model's")
+                mask |= 1 << index[id(p)]
+            seen |= mask
+            k = _sgd_knobs(pg)
+            groups.append((mask, float(pg["lr"]), k["momentum"], k["weight_decay"], k["dampening"], k["nesterov"]))
+        if seen != 0x3FF:
+            raise NotImplementedError("every parameter of the model must be in some param group: torch would leave the "
+                                      "others un-updated, the fused tail updates all ten tensors")
+        key = tuple(groups)
+        if key != self._groups_key:
+            for mask, lr, mom, wd, damp, nest in groups:
+                self.engine.set_sgd_group(mask, lr, mom, wd, damp, nest)
+            self._groups_key = key
+
     def _sync_momentum(self, optimizer, before: bool):
         """`optimizer.state[p]['momentum_buffer']` are views of the library's flat buffer.  Before a step: adopt
         buffers that came from `optimizer.load_state_dict`; after the first executed step: publish the views."""
@@ -330,7 +354,9 @@ class DistributedDataParallel(_tnn.Module):
                                "loss.backward() by optimizer.step()")
         self._optimizer = optimizer
         eng = self._ensure_engine(use_scaler, lr, scaler, sgd, batch=loss.images.shape[0])
-        momentum = bool(sgd and sgd.get("momentum", 0.0) != 0.0 and optimizer is not None)
+        if optimizer is not None and (len(optimizer.param_groups) > 1 or self._groups_key is not None):
+            self._apply_param_groups(optimizer)
+        momentum = optimizer is not None and any(float(pg.get("momentum", 0.0)) != 0.0 for pg in optimizer.param_groups)
         if momentum and optimizer.state:
             # cheap sentinel: only a load_state_dict() since the last step makes the first buffer something else
             # than our view of the library's memory
@@ -419,8 +445,8 @@ class GradScaler:
     def step(self, optimizer):
         params = optimizer.param_groups[0]["params"]
         g = optimizer.param_groups[0]
-        if len(optimizer.param_groups) != 1 or g.get("maximize", False):
-            raise NotImplementedError("the fused step implements torch.optim.SGD with one parameter group, maximize=False")
+        if any(pg.get("maximize", False) for pg in optimizer.param_groups):
+            raise NotImplementedError("the fused step implements torch.optim.SGD with maximize=False")
         owner = getattr(params[0], "_b200_owner", None)
         if owner is None:  # engine not built yet: find the wrapper through the armed loss
             owner = _find_owner(params)

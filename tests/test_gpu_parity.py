@@ -519,6 +519,43 @@ def test_nan_input_poisons_the_step_like_torch():
     e.close()
 
 
+def test_param_groups_match_torch_on_the_same_gradients():
+    """SURVEY 8(f) N3, parameter groups: `ddpstep_set_sgd_group` gives the tensors of each `optimizer.param_groups` entry
+    their own lr / momentum / weight decay / nesterov.  torch.optim.SGD with the same three groups, fed the library's own
+    gradients, must end with bit-identical parameters and momentum buffers; one group's lr is then changed mid-run."""
+    st = _seed_state()
+    e = _engine(dtype="fp16", batch_cap=32, lr=1e-3)
+    e.load_state(st.flat_params().numpy(), _bn_of(st))
+    bounds = [0, 400, 416, 432, 448, 13248, 13280, 13312, 13344, 29024, 29034]  # the ten tensors of the flat vector
+    ps = [torch.nn.Parameter(e.params[bounds[i]:bounds[i + 1]].clone()) for i in range(10)]
+    convs, bns, fc = [ps[0], ps[1], ps[4], ps[5]], [ps[2], ps[3], ps[6], ps[7]], [ps[8], ps[9]]
+    opt = torch.optim.SGD([{"params": convs, "lr": 1e-2, "momentum": 0.9, "nesterov": True},
+                           {"params": bns, "lr": 1e-3},
+                           {"params": fc, "lr": 5e-3, "momentum": 0.5, "dampening": 0.1, "weight_decay": 1e-2}], lr=1e-3)
+    e.set_sgd_group(0b0000110011, 1e-2, momentum=0.9, nesterov=True)
+    e.set_sgd_group(0b0011001100, 1e-3)
+    e.set_sgd_group(0b1100000000, 5e-3, momentum=0.5, dampening=0.1, weight_decay=1e-2)
+    x, y = O.synthetic_mnist(32 * 6)
+    for s in range(6):
+        e.train_step(x[s * 32:(s + 1) * 32].cuda().contiguous(), y[s * 32:(s + 1) * 32].cuda().contiguous())
+        torch.cuda.synchronize()
+        if e.found_inf.item() == 1.0:
+            continue
+        for i, p in enumerate(ps):
+            p.grad = e.grads[bounds[i]:bounds[i + 1]].clone()
+        opt.step()
+        got = e.params.view(torch.int32)
+        for i, p in enumerate(ps):
+            assert torch.equal(got[bounds[i]:bounds[i + 1]], p.detach().view(torch.int32)), f"step {s} tensor {i}"
+        for i in (0, 1, 4, 5, 8, 9):
+            assert torch.equal(e.momentum_buffer[bounds[i]:bounds[i + 1]].view(torch.int32),
+                               opt.state[ps[i]]["momentum_buffer"].view(torch.int32)), f"step {s} buffer {i}"
+        if s == 3:  # an LR scheduler acting on one group only
+            opt.param_groups[2]["lr"] = 1e-3
+            e.set_sgd_group(0b1100000000, 1e-3, momentum=0.5, dampening=0.1, weight_decay=1e-2)
+    e.close()
+
+
 def test_sgd_momentum_trajectory_matches_oracle():
     st = _seed_state()
     kw = dict(lr=1e-3, momentum=0.9, dampening=0.1, weight_decay=1e-3)

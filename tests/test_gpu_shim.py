@@ -250,3 +250,37 @@ def test_torch_ops_are_registered_with_the_dispatcher_and_match_the_engine():
     assert torch.equal(torch.ops.ddp_b200.allreduce_bucket_(t, h), torch.arange(10, dtype=torch.float32, device="cuda"))
     torch_ops.unregister(h)
     a.close(); b.close()
+
+
+def test_shim_accepts_several_param_groups():
+    """`torch.optim.SGD([{...}, {...}])` on the shim model: same bits as the C ABI with `ddpstep_set_sgd_group`."""
+    from ddp_practice_b200 import Engine
+    from ddp_practice_b200.shim import GradScaler, nn
+    torch.manual_seed(3407)
+    model = RefConvNet(torch.float16, "cuda").cuda()
+    init_p, init_bn = flat_params(model).numpy(), bn_buffers(model).numpy()
+    model = nn.parallel.DistributedDataParallel(nn.SyncBatchNorm.convert_sync_batchnorm(model), device_ids=[0])
+    criterion = nn.CrossEntropyLoss().cuda()
+    fc = list(model.module.fc.parameters())
+    rest = [p for n, p in model.module.named_parameters() if not n.startswith("fc.")]
+    optimizer = torch.optim.SGD([{"params": rest, "lr": 1e-2, "momentum": 0.9}, {"params": fc, "lr": 1e-3, "weight_decay": 1e-2}], lr=1e-4)
+    scaler = GradScaler()
+    e = Engine(dtype="fp16", batch_cap=32)
+    e.load_state(init_p, init_bn)
+    e.set_sgd_group(0b0011111111, 1e-2, momentum=0.9)
+    e.set_sgd_group(0b1100000000, 1e-3, weight_decay=1e-2)
+    x, y = O.synthetic_mnist(32 * 4)
+    x, y = x.cuda(), y.cuda()
+    model.train()
+    for s in range(4):
+        xb, yb = x[32 * s:32 * s + 32], y[32 * s:32 * s + 32]
+        loss = criterion(model(xb), yb)
+        optimizer.zero_grad()
+        scaler.scale(loss).backward()
+        scaler.step(optimizer)
+        scaler.update()
+        e.train_step(xb.contiguous(), yb.contiguous())
+        torch.cuda.synchronize()
+        assert torch.equal(flat_params(model), e.params.cpu()), f"step {s}"
+    assert "momentum_buffer" in optimizer.state[rest[0]]
+    e.close()

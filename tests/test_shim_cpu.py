@@ -85,8 +85,10 @@ def test_sgd_hyper_parameters_are_read_from_the_param_group():
                                                                             dampening=0.0, nesterov=False)
     with pytest.raises(NotImplementedError, match="maximize"):
         shim.GradScaler().step(torch.optim.SGD(p, 1e-4, maximize=True))
+    # several param groups are supported (ddpstep_set_sgd_group); an optimizer over parameters that belong to no shim
+    # model is refused before anything is launched
     two = torch.optim.SGD([{"params": p}, {"params": [tnn.Parameter(torch.zeros(2))]}], 1e-4)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(RuntimeError, match="does not hold the parameters"):
         shim.GradScaler().step(two)
 
 
