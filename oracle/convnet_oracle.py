@@ -15,6 +15,7 @@ What it restates (reference = gbbin/DDP-practice, arithmetic lives in torch):
 * DDP Reducer: pre-divide by W then SUM           torch/.../c10d/reducer.hpp:276, default_comm_hooks.hpp:36-51
 * GradScaler scale/unscale_/step/update           torch/amp/grad_scaler.py:193-217,302-373,484-559
 * SGD (momentum 0, wd 0) foreach update           torch/optim/sgd.py:473
+* gradient accumulation under DDP.no_sync()       torch/nn/parallel/distributed.py:1441-1470
 
 The contractions (conv2d / matmul) are delegated to ATen's fp32 CPU kernels on
 operands that were first rounded to the autocast dtype; every other formula
@@ -78,6 +79,9 @@ class OracleState:
     growth_interval: int = 2000
     # torch.optim.SGD state (sgd.py:425-465): flat momentum buffer, created by the first executed step
     momentum_buffer: Optional[torch.Tensor] = None
+    # DDP.no_sync() / gradient accumulation (torch/nn/parallel/distributed.py:1441-1470): what the `.grad` tensors hold
+    # between two optimizer steps when zero_grad() is not called -- one flat fp32 gradient per rank, None when empty
+    grad_accum: Optional[List[torch.Tensor]] = None
 
     @staticmethod
     def from_state_dict(sd: Dict[str, torch.Tensor]) -> "OracleState":
@@ -304,7 +308,8 @@ class StepResult:
 
 def train_step(st: OracleState, xs: Sequence[torch.Tensor], ys: Sequence[torch.Tensor], dtype: str = "fp16",
                use_scaler: bool = True, sync_bn: bool = True, lr: float = 1e-4, momentum: float = 0.0,
-               weight_decay: float = 0.0, dampening: float = 0.0, nesterov: bool = False) -> StepResult:
+               weight_decay: float = 0.0, dampening: float = 0.0, nesterov: bool = False,
+               accumulate: bool = False) -> StepResult:
     """One `train()` iteration on W = len(xs) ranks that share `st` (replicas are
     identical, as DDP guarantees).  Mutates `st` like the reference mutates model,
     optimizer and scaler.  With W > 1, `sync_bn=True` is the reference behaviour
@@ -350,6 +355,15 @@ def train_step(st: OracleState, xs: Sequence[torch.Tensor], ys: Sequence[torch.T
     b2 = bwd_sums([r.head_bwd(scale) for r in ranks], n2)
     b1 = bwd_sums([r.bn2_conv2_bwd(*a) for r, a in zip(ranks, b2)], n1)
     per_rank = [flatten_grads(r.bn1_conv1_bwd(*a)) for r, a in zip(ranks, b1)]
+    # gradient accumulation: autograd ADDS this backward's (rounded, scaled) gradient to what `.grad` already holds, in
+    # fp32.  `accumulate=True` is a backward inside `with model.no_sync():` -- nothing is reduced, unscaled or applied,
+    # BN statistics / running buffers above were updated as in any forward (distributed.py:1441-1470)
+    if st.grad_accum is not None:
+        per_rank = [a + g for a, g in zip(st.grad_accum, per_rank)]
+    if accumulate:
+        st.grad_accum = per_rank
+        return StepResult(losses, float("nan"), per_rank[0].clone(), per_rank[0].clone(), [r.logits for r in ranks])
+    st.grad_accum = None
 
     # DDP Reducer: bucket = grad * (1/W), then all-reduce SUM (rank order here)
     inv_w = torch.tensor(1.0 / W, dtype=torch.float32)

@@ -19,6 +19,9 @@ pinned on outputs of the reference itself:
   origin_fp32_nesterov.npz / amp_fp16_momentum.npz
                     the same two loops with SGD(momentum, weight_decay, dampening / nesterov)
                     (`python tests/golden/make_golden.py sgd` writes only these).
+  amp_fp16_accum.npz
+                    ddp_main.ConvNet, fp16 autocast + GradScaler, TWO backward passes per optimizer step (gradient
+                    accumulation, what DDP.no_sync() does per rank); `... make_golden.py accum` writes only this.
 """
 import contextlib
 import importlib.util
@@ -208,6 +211,46 @@ def gen_test_counts(path, seed=3407):
     np.savez_compressed(path, **out)
 
 
+def gen_amp_accum(path, dtype=torch.float16, batch=8, steps=4, seed=3407):
+    """Gradient accumulation: the reference's model and loop body with TWO backward passes per optimizer
+    step and no zero_grad() in between -- what `with model.no_sync():` around the first one does on every rank."""
+    ref = load_ref("ddp_main")
+    torch.cuda.amp.autocast = lambda: torch.autocast("cpu", dtype=dtype)
+    torch.manual_seed(seed)
+    model = ref.ConvNet()
+    criterion = nn.CrossEntropyLoss()
+    optimizer = torch.optim.SGD(model.parameters(), 1e-4)
+    scaler = torch.amp.GradScaler("cpu")
+    x, y = synthetic_mnist(batch * steps * 2)
+    out = sd_arrays(model, "init_")
+    out["x"], out["y"] = x.numpy(), y.numpy()
+    losses, scales, trackers, founds, grads = [], [], [], [], []
+    model.train()
+    for s in range(steps):
+        optimizer.zero_grad()
+        for m in range(2):
+            lo = (2 * s + m) * batch
+            loss = criterion(model(x[lo:lo + batch]), y[lo:lo + batch])
+            scaler.scale(loss).backward()
+            losses.append(loss.item())
+        scaler.unscale_(optimizer)
+        g = flat_grads(model)
+        founds.append(0.0 if np.isfinite(g).all() else 1.0)
+        grads.append(np.nan_to_num(g, nan=0.0, posinf=0.0, neginf=0.0))
+        scaler.step(optimizer)
+        scaler.update()
+        scales.append(scaler.get_scale())
+        trackers.append(int(scaler._growth_tracker.item()))
+    out["losses"] = np.array(losses, dtype=np.float64)
+    out["scales"] = np.array(scales, dtype=np.float64)
+    out["trackers"] = np.array(trackers, dtype=np.int64)
+    out["found_inf"] = np.array(founds, dtype=np.float64)
+    out["grads"] = np.stack(grads)
+    out.update(sd_arrays(model, "final_"))
+    out["batch"], out["steps"] = np.int64(batch), np.int64(steps)
+    np.savez_compressed(path, **out)
+
+
 def gen_sgd_knobs():
     """the reference's model / loop body with the other torch.optim.SGD knobs switched on (the
     reference itself only ever passes lr; the optimizer class is the same)."""
@@ -223,6 +266,9 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["sgd"]:  # only the N3 vectors (leaves the others byte-identical)
         gen_sgd_knobs()
         raise SystemExit(0)
+    if sys.argv[1:] == ["accum"]:
+        gen_amp_accum(os.path.join(HERE, "amp_fp16_accum.npz"))
+        raise SystemExit(0)
     gen_origin(os.path.join(HERE, "origin_fp32.npz"), batch=8, steps=3)
     gen_origin(os.path.join(HERE, "global_w4.npz"), batch=32, steps=2)
     gen_amp(os.path.join(HERE, "amp_fp16.npz"), torch.float16)
@@ -230,6 +276,7 @@ if __name__ == "__main__":
     gen_test_counts(os.path.join(HERE, "test_counts.npz"))
     gen_gloo(os.path.join(HERE, "ddp_gloo_w2.npz"))
     gen_sgd_knobs()
+    gen_amp_accum(os.path.join(HERE, "amp_fp16_accum.npz"))
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

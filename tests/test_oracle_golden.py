@@ -214,3 +214,26 @@ def test_momentum_update_is_world_size_invariant_under_syncbn():
         O.train_step(b, list(x.chunk(4)), list(y.chunk(4)), dtype="fp32", use_scaler=False, sync_bn=True, **kw)
     assert_grads_close(a.momentum_buffer, b.momentum_buffer, 2e-5, "momentum buffer W=1 vs W=4")
     assert torch.allclose(a.flat_params(), b.flat_params(), rtol=1e-5, atol=1e-6)
+
+
+def test_amp_fp16_gradient_accumulation_matches_reference():
+    """SURVEY 8(f) N3, `no_sync` / gradient accumulation: the reference's model with two backward passes per optimizer
+    step (vectors made by tests/golden/make_golden.py from /root/reference/ddp_main.py) against the oracle's
+    `accumulate=True` micro-step followed by an ordinary step -- the same pair the CUDA path is held to on the GPU
+    (tests/test_gpu_parity.py::test_gradient_accumulation_matches_torch)."""
+    g = load_golden("amp_fp16_accum.npz")
+    B, S = int(g["batch"]), int(g["steps"])
+    x, y = torch.from_numpy(g["x"]), torch.from_numpy(g["y"])
+    st, ini = state_from_golden(g), state_from_golden(g)
+    for s in range(S):
+        lo = 2 * s * B
+        r1 = O.train_step(st, [x[lo:lo + B]], [y[lo:lo + B]], dtype="fp16", accumulate=True)
+        assert st.grad_accum is not None and r1.losses[0] == pytest.approx(g["losses"][2 * s], rel=AMP_TOL)
+        r = O.train_step(st, [x[lo + B:lo + 2 * B]], [y[lo + B:lo + 2 * B]], dtype="fp16")
+        assert st.grad_accum is None and r.losses[0] == pytest.approx(g["losses"][2 * s + 1], rel=AMP_TOL)
+        assert r.found_inf == g["found_inf"][s] and st.scale == g["scales"][s] and st.growth_tracker == g["trackers"][s]
+        if r.found_inf == 0.0:
+            assert_grads_close(r.grads, g["grads"][s], AMP_TOL, f"accumulated step {s}")
+    assert st.num_batches_tracked == [2 * S, 2 * S]  # every forward, synchronising or not, counts a batch
+    fin = state_from_golden(g, "final_")
+    assert_grads_close(st.flat_params() - ini.flat_params(), fin.flat_params() - ini.flat_params(), AMP_TOL, "update")
