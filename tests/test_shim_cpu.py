@@ -115,3 +115,41 @@ def test_config_struct_mirrors_the_header():
     cfg = _lib.Config()
     _lib.load().ddpstep_default_config(cfg)
     assert cfg.abi_version == 3 and cfg.momentum == 0.0 and cfg.nesterov == 0 and abs(cfg.lr - 1e-4) < 1e-10
+
+
+def test_c_abi_argument_errors_need_no_gpu():
+    """Every entry point validates its arguments before it touches CUDA, so the error paths can be exercised here:
+    bad world size / ABI version / optimizer knobs at create time, and the allocation-free entry point's null,
+    alignment and size checks (its message names the 1024-image limit)."""
+    import ctypes as C
+    from ddp_practice_b200 import _lib
+    lib = _lib.load()
+    cfg = _lib.Config()
+    lib.ddpstep_default_config(C.byref(cfg))
+    ctx = C.c_void_p()
+    cfg.world, cfg.rank = 9, 0
+    assert lib.ddpstep_create(C.byref(cfg), C.byref(ctx)) == -1 and b"world" in lib.ddpstep_last_error(None)
+    lib.ddpstep_default_config(C.byref(cfg))
+    cfg.abi_version = 1
+    assert lib.ddpstep_create(C.byref(cfg), C.byref(ctx)) == -1 and b"ABI" in lib.ddpstep_last_error(None)
+    lib.ddpstep_default_config(C.byref(cfg))
+    cfg.nesterov = 1  # without momentum: torch/optim/sgd.py:68 raises too
+    assert lib.ddpstep_create(C.byref(cfg), C.byref(ctx)) == -1 and b"nesterov" in lib.ddpstep_last_error(None)
+    lib.ddpstep_default_config(C.byref(cfg))
+    cfg.batch_cap = 0
+    assert lib.ddpstep_create(C.byref(cfg), C.byref(ctx)) == -1
+    # allocation-free entry point: fake but well-formed addresses, nothing is dereferenced before the checks
+    a16 = 0x10000
+    call = lib.ddpstep_conv1_bnstats_noalloc
+    assert call(None, a16, 8, 1, 1, 1e-5, a16, a16, None) == -1 and b"null" in lib.ddpstep_last_error(None)
+    assert call(a16, a16, 8, 7, 1, 1e-5, a16, a16, None) == -1 and b"dtype" in lib.ddpstep_last_error(None)
+    assert call(a16, a16 + 4, 8, 1, 1, 1e-5, a16, a16, None) == -1 and b"aligned" in lib.ddpstep_last_error(None)
+    assert call(a16, a16, 8, 1, 1, 1e-5, a16, a16 + 2, None) == -1 and b"aligned" in lib.ddpstep_last_error(None)
+    assert call(a16, a16, 1025, 1, 1, 1e-5, a16, a16, None) == -1 and b"1024" in lib.ddpstep_last_error(None)
+    assert call(a16, a16, 0, 1, 1, 1e-5, a16, a16, None) == -1
+    # null contexts are refused, not dereferenced
+    assert lib.ddpstep_train_step(None, a16, a16, 8, None) == -1
+    assert lib.ddpstep_set_sgd_group(None, 1, 1e-3, 0.0, 0.0, 0.0, 0, None) == -1
+    assert lib.ddpstep_allreduce_bucket(None, a16, 8, 1, None) == -1
+    assert lib.ddpstep_launch_count(None) == 0 and lib.ddpstep_destroy(None) == 0
+    assert lib.ddpstep_kernel_name(14) == b"step" and lib.ddpstep_kernel_name(99) == b""
