@@ -240,6 +240,7 @@ class DistributedDataParallel(_tnn.Module):
         sd_b["layer1.1.num_batches_tracked"].data = eng.num_batches_tracked[0]
         sd_b["layer2.1.num_batches_tracked"].data = eng.num_batches_tracked[1]
         self.engine, self._engine_key = eng, key
+        self._groups_key = None  # a new context starts with the first group's settings everywhere: re-send the others
         if carry is not None:
             self._mom_published = False  # optimizer.state views point into the old context: re-publish
         return eng
