@@ -7,7 +7,18 @@
 
 Workload (config.workload): BASELINE.json configs[1] -- "ddp_main.py ConvNet with AMP autocast
 + GradScaler, batch 32/GPU" (fp16, SyncBN + DDP all-reduce when N > 1).  A step is one pass of
-ddp_main.py:86-93 over one batch of synthetic MNIST-shaped input.  Prints ONE JSON line."""
+ddp_main.py:86-93 over one batch of synthetic MNIST-shaped input.  Prints ONE JSON line:
+
+  value / ms_per_step   K steps, inputs resident in HBM, through ddpstep_train_steps (min(K, 50) steps per graph launch)
+  per_step_launch       the same K steps as one ddpstep_train_step call (one graph launch) each; p50_step_us likewise
+  e2e                   pinned HOST batch in, loss out, every step, through ddpstep_train_step_host
+  roofline              dominant kernel (event nodes inside the step graph), latency floor, ncu dram traffic
+  parity_checks         GradScaler state vs the reference's data-independent trajectory; replicas bit-identical (N > 1)
+  allreduce (N > 1)     the 116,136-byte bucket: bare exchange, fused tail, eager NCCL
+  large_batch           BASELINE.json configs[3]: bf16, batch 4096 per GPU, 20 steps
+  input_pipeline        the step fed from a GPU-resident uint8 dataset by DistributedSampler indices
+  cpu_baseline (N = 1)  origin_main.py's fp32 step on the host cores (also `--impl reference`)
+Timing scheme: DESIGN.md section 7."""
 import argparse
 import json
 import os
